@@ -1,0 +1,198 @@
+/* b200spmv.h -- the C ABI under the LIBSPMV plugin boundary, B200 (sm_100a).
+ *
+ * Every entry point here is what a backend of the reference has to provide
+ * behind `spmv::DeviceExecutor` / `spmv::CSRSpMV<T>` / `spmv::L2GMap` /
+ * `spmv::cg` (reference file:line cited per function).  Conventions:
+ *   - plain C types only; `d_` pointers are device pointers on the current
+ *     CUDA device; `stream` is a cudaStream_t passed as void* (NULL = legacy
+ *     default stream); nothing here synchronises the host unless it says so;
+ *   - every function returns 0 on success or a negative B200_E* code, and
+ *     `b200_last_error()` gives a thread-local message.  The C++ host layer
+ *     (include/spmv/) turns non-zero into std::runtime_error, the way the
+ *     reference's constructors throw (Matrix.cpp:29, L2GMap.cpp:363);
+ *   - there is no CPU fallback: without a usable GPU every compute call
+ *     returns B200_ECUDA.
+ */
+#ifndef B200SPMV_H
+#define B200SPMV_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+#define B200_OK 0
+#define B200_EINVAL (-1) /* bad argument */
+#define B200_ECUDA (-2)  /* CUDA runtime / launch failure, or no device */
+#define B200_ENCCL (-3)  /* NCCL failure or NCCL not loadable */
+#define B200_ENOMEM (-4)
+
+B200_API const char* b200_last_error(void);
+/* ABI version of this header: bump on any signature change. */
+B200_API int b200_abi_version(void);
+
+/* ---- device memory and streams: DeviceExecutor::_alloc/_free/_memset/_copy*
+ *      (device_executor.h:129-139; cuda/cuda_executor.cpp:54-105) ---------- */
+B200_API int b200_device_count(int* count);
+B200_API int b200_set_device(int device_id);
+B200_API int b200_get_num_sms(int* num_sms); /* DeviceExecutor::get_num_cus (device_executor.h:85) */
+B200_API int b200_malloc(void** d_ptr, size_t num_bytes);
+B200_API int b200_free(void* d_ptr);
+B200_API int b200_memset_async(void* d_ptr, int value, size_t num_bytes, void* stream);
+B200_API int b200_memcpy_d2d_async(void* d_dst, const void* d_src, size_t num_bytes, void* stream);
+B200_API int b200_memcpy_h2d_async(void* d_dst, const void* h_src, size_t num_bytes, void* stream);
+B200_API int b200_memcpy_d2h_async(void* h_dst, const void* d_src, size_t num_bytes, void* stream);
+B200_API int b200_host_alloc_pinned(void** h_ptr, size_t num_bytes);
+B200_API int b200_host_free_pinned(void* h_ptr);
+B200_API int b200_stream_create(void** stream);
+B200_API int b200_stream_destroy(void* stream);
+B200_API int b200_stream_synchronize(void* stream); /* DeviceExecutor::synchronize (device_executor.h:82) */
+B200_API int b200_event_create(void** event, int timing);
+B200_API int b200_event_destroy(void* event);
+B200_API int b200_event_record(void* event, void* stream);
+B200_API int b200_event_synchronize(void* event);
+B200_API int b200_stream_wait_event(void* stream, void* event);
+B200_API int b200_event_elapsed_ms(void* start, void* stop, float* ms);
+
+/* ---- CSR SpMV plan: CSRSpMV<T>::init / finalize (csr_kernels.h:71-78,
+ *      csr_kernels.cpp:11-17,55-57; the reference hangs its analysis off
+ *      `void* _aux_data`, csr_kernels.h:82).  The plan cuts the rows into
+ *      tiles of bounded matrix-stream bytes and takes the row-length histogram
+ *      that selects the thread-per-row / warp-per-row walks.  `d_rowptr` may be NULL iff
+ *      nnz == 0 (csr_matrix.cpp:35).  Synchronises `stream` once. ---------- */
+B200_API int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
+                         const int32_t* d_rowptr, int symmetric, void* stream);
+B200_API int b200_csr_plan_destroy(void* plan);
+/* Introspection (tests, bench): number of tiles and the row-length histogram
+ * (bucket k counts rows with length in [2^(k-1), 2^k), bucket 0 = empty rows;
+ * 32 buckets). */
+B200_API int b200_csr_plan_info(void* plan, int32_t* num_tiles, int32_t* max_row_len,
+                       int64_t hist[32]);
+/* Tuning hook (bench sweeps): variant 0 = persistent CTAs with a bulk-async
+ * staged ring (default), 1 = one tile per CTA staged with plain loads.
+ * Re-partitions the tiles when tile_bytes changes (needs the same d_rowptr the
+ * plan was created with).  Defaults also read B200_SPMV_{VARIANT,TILE_BYTES,
+ * STAGES,CWARPS,CTAS} from the environment at plan creation. */
+B200_API int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int tile_bytes,
+                       int stages, int consumer_warps, int ctas_per_sm, void* stream);
+
+/* ---- general CSR SpMV: CSRSpMV<T>::run, general branch
+ *      (csr_kernels.cpp:41-51; replaces cusparseSpMV at
+ *      cuda/csr_kernels.cuda.cu:106-151).
+ *      y[i] = alpha * sum_j val[j]*x[col[j]] + beta*y[i], j ascending.
+ *      beta == 0 means overwrite (y is not read). ------------------------- */
+B200_API int b200_csr_spmv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const double* d_val, double alpha, const double* d_x, double beta,
+                      double* d_y, void* stream);
+B200_API int b200_csr_spmv_f32(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const float* d_val, float alpha, const float* d_x, float beta,
+                      float* d_y, void* stream);
+/* Same, and additionally d_dot[0] = sum_i x[i]*y[i] over the rows (the p.Ap of
+ * cg.cpp:63 riding in the SpMV epilogue); deterministic two-stage reduction. */
+B200_API int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                          const double* d_val, const double* d_x, double* d_y,
+                          double* d_dot, void* stream);
+
+/* ---- symmetric CSR SpMV: CSRSpMV<T>::run, symmetric branch
+ *      (csr_kernels.cpp:26-40; replaces csr_sym_gmem_atomics at
+ *      cuda/csr_kernels.cuda.cu:22-47,87-105).  Stored: strictly lower triangle
+ *      of the local diagonal block (col < row) + `d_diag[rows]`.
+ *      y = alpha*(L + D + L^T) x + beta*y.  d_rowptr/d_colind/d_val may be NULL
+ *      iff the plan's nnz == 0 (diagonal-only block, csr_matrix.cpp:85). --- */
+B200_API int b200_csr_symv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const double* d_val, const double* d_diag, double alpha,
+                      const double* d_x, double beta, double* d_y, void* stream);
+B200_API int b200_csr_symv_f32(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const float* d_val, const float* d_diag, float alpha,
+                      const float* d_x, float beta, float* d_y, void* stream);
+
+/* ---- halo pack / unpack: DeviceExecutor::gather_ghosts_run
+ *      (device_executor.h:123-126; cuda/cuda_executor.cu:9-51) and the
+ *      accumulate loop of L2GMap::reverse_update (L2GMap.cpp:920-921). ----- */
+B200_API int b200_gather_f64(int32_t n, const int32_t* d_idx, const double* d_in, double* d_out, void* stream);
+B200_API int b200_gather_f32(int32_t n, const int32_t* d_idx, const float* d_in, float* d_out, void* stream);
+B200_API int b200_scatter_add_f64(int32_t n, const int32_t* d_idx, const double* d_in, double* d_inout, void* stream);
+B200_API int b200_scatter_add_f32(int32_t n, const int32_t* d_idx, const float* d_in, float* d_inout, void* stream);
+
+/* ---- NCCL communicator and halo exchange: the message part of
+ *      L2GMap::update_p2p / update_p2p_start (L2GMap.cpp:564-635) and of
+ *      reverse_update_p2p (:924-950).  One rank per GPU.
+ *      b200_halo_exchange posts, in one NCCL group on `comm_stream`, for each
+ *      neighbour i: send d_sendbuf[send_off[i] .. +send_cnt[i]) and receive
+ *      recv_cnt[i] values into d_recvbuf[recv_off[i] ..).  Counts are elements
+ *      of `elem_bytes` (4 or 8). ------------------------------------------- */
+#define B200_NCCL_UNIQUE_ID_BYTES 128
+B200_API int b200_nccl_unique_id(char id[B200_NCCL_UNIQUE_ID_BYTES]);
+B200_API int b200_nccl_comm_create(void** comm, int nranks, int rank, const char id[B200_NCCL_UNIQUE_ID_BYTES]);
+B200_API int b200_nccl_comm_destroy(void* comm);
+B200_API int b200_halo_exchange(void* comm, int nnbr, const int32_t* nbr_rank, const void* d_sendbuf,
+                       const int32_t* send_cnt, const int32_t* send_off, void* d_recvbuf,
+                       const int32_t* recv_cnt, const int32_t* recv_off, int elem_bytes,
+                       void* comm_stream);
+/* In-stream sum-allreduce of n doubles (MPI_Allreduce at cg.cpp:49,65,75). */
+B200_API int b200_allreduce_sum_f64(void* comm, double* d_inout, int32_t n, void* stream);
+
+/* ---- CG building blocks: cg.cpp:47-85 (cblas_ddot/daxpy/dscal) and the
+ *      scalar kernels of cuda/cg.cuda.cu:14-38, fused.  All scalars live in a
+ *      device "state" block of B200_CG_STATE_DOUBLES doubles so the loop never
+ *      needs the host:
+ *        st[0] rnorm_old   st[1] p.Ap (global)   st[2] r.r (global, raw sum)
+ *        st[3] rnorm0      st[4] done flag (0/1) st[5] iterations completed
+ *        st[6] rtol        st[7] kmax            st[16..] reduction scratch
+ *      Every kernel is a no-op once st[4] != 0, so a fixed-length CUDA graph of
+ *      iterations reproduces the reference's early exit (cg.cpp:80-81).
+ *      Reductions are deterministic (fixed grid, fixed-order tree). -------- */
+#define B200_CG_STATE_DOUBLES 4096
+#define B200_DOT_SCRATCH_DOUBLES 2048
+/* d_out[0] = sum a[i]*b[i].  d_scratch: B200_DOT_SCRATCH_DOUBLES doubles, zeroed
+ * once by the caller before first use.  If d_done_flag != NULL and
+ * *d_done_flag != 0 the kernel does nothing. */
+B200_API int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, double* d_out,
+                    double* d_scratch, const double* d_done_flag, void* stream);
+/* st[0] = st[3] = sqrt(d_rr[0]) (d_rr = allreduced r.r, cg.cpp:47-53); clears
+ * done / iteration count; stores rtol and kmax. */
+B200_API int b200_cg_init_state(double* d_state, const double* d_rr, double rtol, int32_t kmax, void* stream);
+/* alpha = st[0]^2/st[1];  x += alpha p;  r -= alpha Ap;  st[2] = r.r (local
+ * part; the caller allreduces st[2] in place when there is more than one rank).
+ * cg.cpp:66-73. */
+B200_API int b200_cg_update_xr_f64(int32_t n, double* d_state, const double* d_p, const double* d_Ap,
+                          double* d_x, double* d_r, void* stream);
+/* After the allreduce of st[2]: rnorm_new = sqrt(st[2]); beta = rnorm_new^2 /
+ * st[0]^2; unless rnorm_new/st[3] < rtol: p = beta p + r (cg.cpp:76-85).  Then
+ * iterations += 1, d_hist[iterations-1] = rnorm_new (if d_hist != NULL and in
+ * range), st[0] = rnorm_new, done = converged || iterations == kmax. */
+B200_API int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* d_p,
+                         double* d_hist, int32_t hist_len, void* stream);
+
+/* ---- synthetic operators generated on the device (bench / tests only; the
+ *      host builders create_A, create_matrix, read_petsc are in include/spmv/).
+ *      3-D Laplacian on an nx*ny*nzg grid, index i = x + nx*(y + ny*z), rows
+ *      z in [z0, z1) owned; stencil 7 (diag 6, nbrs -1) or 27 (diag 26, nbrs
+ *      -1), Dirichlet truncation.  Column numbering is the local one of
+ *      Matrix.cpp:294-318: owned g - nx*ny*z0, ghosts (plane z0-1 then plane
+ *      z1) ascending after the owned block; rows sorted by local column.
+ *      mode 0: one general block;  mode 1: symmetric split (strictly lower
+ *      local block + diagonal + remote block, Matrix.cpp:337-349);  mode 2:
+ *      overlap split (local block + remote block, Matrix.cpp:350-355).
+ *      Step 1 fills the row pointers (rows+1 ints each) and returns the entry
+ *      counts (synchronises); step 2 fills the arrays the caller then sized. -- */
+B200_API int b200_gen_laplace3d_rowptr(int nx, int ny, int64_t nzg, int64_t z0, int64_t z1, int stencil,
+                              int mode, int32_t* d_rowptr_local, int32_t* d_rowptr_remote,
+                              int64_t* nnz_local, int64_t* nnz_remote, void* stream);
+B200_API int b200_gen_laplace3d_fill(int nx, int ny, int64_t nzg, int64_t z0, int64_t z1, int stencil,
+                            int mode, const int32_t* d_rowptr_local, int32_t* d_colind_local,
+                            double* d_val_local, double* d_diag, const int32_t* d_rowptr_remote,
+                            int32_t* d_colind_remote, double* d_val_remote, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPMV_H */

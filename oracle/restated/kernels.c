@@ -1,0 +1,113 @@
+/* oracle/restated/kernels.c -- TEST INFRASTRUCTURE, not product code.
+ *
+ * Plain-C restatement of the reference's per-rank CPU arithmetic for the hot
+ * path.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg
+ * may load this; the product (spmv_b200/, include/) never does.
+ * Pinned against the reference's own compiled csr_kernels.cpp (oracle/_ref) and
+ * the golden values of SURVEY.md Appendix D by tests/test_oracle.py.
+ * Compile without FMA contraction (-ffp-contract=off) so that the result does
+ * not depend on the host ISA.
+ */
+#include <stdint.h>
+#include <stddef.h>
+
+/* csr_kernels.cpp:41-51 -- general branch of CSRSpMV<T>::run */
+void oracle_csr_spmv_f64(int32_t num_rows, const int32_t* rowptr, const int32_t* colind,
+                         const double* values, double alpha, const double* in, double beta,
+                         double* out)
+{
+  for (int32_t i = 0; i < num_rows; ++i) {
+    double sum = 0.0;
+    for (int32_t j = rowptr[i]; j < rowptr[i + 1]; ++j)
+      sum += values[j] * in[colind[j]];
+    out[i] = alpha * sum + beta * out[i];
+  }
+}
+
+void oracle_csr_spmv_f32(int32_t num_rows, const int32_t* rowptr, const int32_t* colind,
+                         const float* values, float alpha, const float* in, float beta, float* out)
+{
+  for (int32_t i = 0; i < num_rows; ++i) {
+    float sum = 0.0f;
+    for (int32_t j = rowptr[i]; j < rowptr[i + 1]; ++j)
+      sum += values[j] * in[colind[j]];
+    out[i] = alpha * sum + beta * out[i];
+  }
+}
+
+/* csr_kernels.cpp:26-40 -- symmetric branch: strictly lower triangle + diagonal.
+ * num_non_zeros == 0 (rowptr may be NULL) leaves only the diagonal term. */
+void oracle_csr_symv_f64(int32_t num_rows, int64_t num_non_zeros, const int32_t* rowptr,
+                         const int32_t* colind, const double* values, const double* diagonal,
+                         double alpha, const double* in, double beta, double* out)
+{
+  for (int32_t i = 0; i < num_rows; ++i) {
+    double sum = diagonal[i] * in[i];
+    if (num_non_zeros > 0) {
+      for (int32_t j = rowptr[i]; j < rowptr[i + 1]; ++j) {
+        int32_t col = colind[j];
+        double val = values[j];
+        sum += val * in[col];
+        out[col] += alpha * val * in[i];
+      }
+    }
+    out[i] = alpha * sum + beta * out[i];
+  }
+}
+
+void oracle_csr_symv_f32(int32_t num_rows, int64_t num_non_zeros, const int32_t* rowptr,
+                         const int32_t* colind, const float* values, const float* diagonal,
+                         float alpha, const float* in, float beta, float* out)
+{
+  for (int32_t i = 0; i < num_rows; ++i) {
+    float sum = diagonal[i] * in[i];
+    if (num_non_zeros > 0) {
+      for (int32_t j = rowptr[i]; j < rowptr[i + 1]; ++j) {
+        int32_t col = colind[j];
+        float val = values[j];
+        sum += val * in[col];
+        out[col] += alpha * val * in[i];
+      }
+    }
+    out[i] = alpha * sum + beta * out[i];
+  }
+}
+
+/* reference_executor.cpp:158-164 -- gather_ghosts_run */
+void oracle_gather_f64(int32_t n, const int32_t* indices, const double* in, double* out)
+{
+  for (int32_t i = 0; i < n; ++i)
+    out[i] = in[indices[i]];
+}
+
+/* L2GMap.cpp:920-921 -- accumulate loop of reverse_update */
+void oracle_scatter_add_f64(int32_t n, const int32_t* indices, const double* in, double* inout)
+{
+  for (int32_t i = 0; i < n; ++i)
+    inout[indices[i]] += in[i];
+}
+
+/* cg.cpp:47,63,73 -- cblas_ddot with unit strides.  The reference's BLAS is an
+ * un-vendored, un-pinned system library (CMakeLists.txt:71); its summation
+ * order is unknown.  This restatement fixes the order: left to right. */
+double oracle_ddot(int32_t n, const double* x, const double* y)
+{
+  double s = 0.0;
+  for (int32_t i = 0; i < n; ++i)
+    s += x[i] * y[i];
+  return s;
+}
+
+/* cg.cpp:69,70,85 -- cblas_daxpy: y += a*x */
+void oracle_daxpy(int32_t n, double a, const double* x, double* y)
+{
+  for (int32_t i = 0; i < n; ++i)
+    y[i] += a * x[i];
+}
+
+/* cg.cpp:84 -- cblas_dscal: x *= a */
+void oracle_dscal(int32_t n, double a, double* x)
+{
+  for (int32_t i = 0; i < n; ++i)
+    x[i] *= a;
+}

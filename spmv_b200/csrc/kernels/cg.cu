@@ -1,0 +1,254 @@
+// cg.cu -- fused vector kernels of the Conjugate Gradient iteration.
+//
+// Replaces the BLAS-1 calls of cg.cpp:47-85 (cblas_ddot / daxpy / dscal; on the
+// reference's CUDA backend cublasDdot x3, cublasDaxpy x3, cublasDscal x1 and the
+// <<<1,1>>> scalar kernels compute_alpha / compute_beta / compute_sqrt,
+// cuda/cg.cuda.cu:14-38,88-150) with three single-pass kernels:
+//   dot        : s = a.b                                   (2 reads)
+//   update_xr  : x += alpha p; r -= alpha Ap; rr = r.r      (4 reads, 2 writes)
+//   update_p   : p = r + beta p  (+ scalar bookkeeping)     (2 reads, 1 write)
+// All scalars stay in a device state block, so the loop never syncs with the
+// host; once the `done` flag is set every kernel is a no-op, which lets a
+// fixed-length CUDA graph reproduce the reference's early exit (cg.cpp:80-81).
+// Reductions are deterministic: fixed grid, per-thread strided partial, warp
+// xor-tree, per-CTA partial, last CTA folds the partials in index order.
+// Element-wise arithmetic is un-contracted (mul then add) like the oracle's
+// plain-loop restatement of daxpy/dscal.
+#include "common.cuh"
+
+#include <algorithm>
+
+namespace b200
+{
+
+// state block layout (doubles), see b200spmv.h
+enum { ST_RNORM_OLD = 0, ST_PAP = 1, ST_RR = 2, ST_RNORM0 = 3, ST_DONE = 4, ST_ITER = 5,
+       ST_RTOL = 6, ST_KMAX = 7, ST_COUNTER = 16, ST_PARTIALS = 32 };
+
+constexpr int VEC_THREADS = 256;
+
+static int vec_grid(int n)
+{
+  const int want = (n + VEC_THREADS * 4 - 1) / (VEC_THREADS * 4);
+  const int cap = std::min(num_sms() * 8, B200_CG_STATE_DOUBLES - ST_PARTIALS);
+  return std::max(1, std::min(want, cap));
+}
+
+// Fold one double per thread over the whole grid into out[0] (deterministic).
+__device__ __forceinline__ bool grid_sum(double v, double* partials, unsigned int* counter,
+                                         double* out)
+{
+  __shared__ double s_warp[VEC_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0)
+    s_warp[warp] = v;
+  __syncthreads();
+  bool last = false;
+  if (warp == 0) {
+    unsigned int ticket = 0;
+    if (lane == 0) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < VEC_THREADS / 32; ++w)
+        t += s_warp[w];
+      partials[blockIdx.x] = t;
+      __threadfence();
+      ticket = atomicAdd(counter, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) {
+      __threadfence();
+      double s = 0.0;
+      for (int i = lane; i < (int)gridDim.x; i += 32)
+        s += __ldcg(partials + i);
+      s = warp_sum(s);
+      if (lane == 0) {
+        out[0] = s;
+        *counter = 0u;
+      }
+      last = true;
+    }
+  }
+  return last;
+}
+
+__global__ void __launch_bounds__(VEC_THREADS)
+    dot_kernel(int n, const double* __restrict__ a, const double* __restrict__ b,
+               double* __restrict__ out, double* __restrict__ scratch, const double* done_flag)
+{
+  if (done_flag != nullptr && *done_flag != 0.0)
+    return;
+  double acc = 0.0;
+  const int stride = gridDim.x * blockDim.x;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n2 = n >> 1;
+  const double2* a2 = reinterpret_cast<const double2*>(a);
+  const double2* b2 = reinterpret_cast<const double2*>(b);
+  for (int i = tid; i < n2; i += stride) {
+    const double2 u = __ldg(a2 + i), w = __ldg(b2 + i);
+    acc = fma(u.x, w.x, acc);
+    acc = fma(u.y, w.y, acc);
+  }
+  if ((n & 1) && tid == 0)
+    acc = fma(a[n - 1], b[n - 1], acc);
+  grid_sum(acc, scratch + 8, reinterpret_cast<unsigned int*>(scratch), out);
+}
+
+// Unaligned fallback (pointer not 16-byte aligned): scalar loads.
+__global__ void __launch_bounds__(VEC_THREADS)
+    dot_kernel_scalar(int n, const double* __restrict__ a, const double* __restrict__ b,
+                      double* __restrict__ out, double* __restrict__ scratch,
+                      const double* done_flag)
+{
+  if (done_flag != nullptr && *done_flag != 0.0)
+    return;
+  double acc = 0.0;
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    acc = fma(__ldg(a + i), __ldg(b + i), acc);
+  grid_sum(acc, scratch + 8, reinterpret_cast<unsigned int*>(scratch), out);
+}
+
+__global__ void init_state_kernel(double* st, const double* rr, double rtol, int kmax)
+{
+  const double rnorm0 = sqrt(rr[0]); // cg.cpp:50
+  st[ST_RNORM_OLD] = rnorm0;         // cg.cpp:53
+  st[ST_RNORM0] = rnorm0;
+  st[ST_PAP] = 0.0;
+  st[ST_RR] = rr[0];
+  st[ST_DONE] = (kmax <= 0) ? 1.0 : 0.0;
+  st[ST_ITER] = 0.0;
+  st[ST_RTOL] = rtol;
+  st[ST_KMAX] = (double)kmax;
+  *reinterpret_cast<unsigned int*>(st + ST_COUNTER) = 0u;
+}
+
+__global__ void __launch_bounds__(VEC_THREADS)
+    update_xr_kernel(int n, double* __restrict__ st, const double* __restrict__ p,
+                     const double* __restrict__ Ap, double* __restrict__ x, double* __restrict__ r)
+{
+  if (st[ST_DONE] != 0.0)
+    return;
+  const double rn = st[ST_RNORM_OLD];
+  const double alpha = (rn * rn) / st[ST_PAP]; // cg.cpp:66
+  const double nalpha = -alpha;
+  double acc = 0.0;
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double pi = p[i], api = Ap[i];
+    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, pi));          // cg.cpp:69
+    const double ri = __dadd_rn(r[i], __dmul_rn(nalpha, api)); // cg.cpp:70
+    r[i] = ri;
+    acc = fma(ri, ri, acc);                                // cg.cpp:73
+  }
+  grid_sum(acc, st + ST_PARTIALS, reinterpret_cast<unsigned int*>(st + ST_COUNTER), st + ST_RR);
+}
+
+__global__ void __launch_bounds__(VEC_THREADS)
+    update_p_kernel(int n, double* __restrict__ st, const double* __restrict__ r,
+                    double* __restrict__ p, double* __restrict__ hist, int hist_len)
+{
+  if (st[ST_DONE] != 0.0)
+    return;
+  const double rnorm_old = st[ST_RNORM_OLD];
+  const double rnorm_new = sqrt(st[ST_RR]);                                  // cg.cpp:76
+  const double beta = (rnorm_new * rnorm_new) / (rnorm_old * rnorm_old);     // cg.cpp:77
+  const bool converged = (rnorm_new / st[ST_RNORM0]) < st[ST_RTOL];          // cg.cpp:80
+  if (!converged) {
+    const int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+      p[i] = __dadd_rn(__dmul_rn(beta, p[i]), r[i]);                         // cg.cpp:84-85
+  }
+  // the last CTA to get here advances the scalars (nobody reads them after this)
+  __shared__ bool s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned int* counter = reinterpret_cast<unsigned int*>(st + ST_COUNTER);
+    const unsigned int ticket = atomicAdd(counter, 1u);
+    s_last = (ticket == gridDim.x - 1);
+    if (s_last) {
+      *counter = 0u;
+      const int iter = (int)st[ST_ITER] + 1;
+      st[ST_ITER] = (double)iter;
+      if (hist != nullptr && iter - 1 < hist_len)
+        hist[iter - 1] = rnorm_new;
+      st[ST_RNORM_OLD] = rnorm_new;                                          // cg.cpp:78
+      if (converged || iter >= (int)st[ST_KMAX])
+        st[ST_DONE] = 1.0;
+    }
+  }
+}
+
+static int need_gpu()
+{
+  if (num_sms() <= 0) {
+    set_error("no CUDA device available: this build has no CPU path");
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, double* d_out,
+                    double* d_scratch, const double* d_done_flag, void* stream)
+{
+  B200_REQUIRE(n >= 0 && d_out && d_scratch, "bad argument");
+  B200_REQUIRE(n == 0 || (d_a && d_b), "NULL vector");
+  if (int rc = need_gpu())
+    return rc;
+  const int grid = std::min(vec_grid(n), B200_DOT_SCRATCH_DOUBLES - 8);
+  const bool al = ((reinterpret_cast<uintptr_t>(d_a) | reinterpret_cast<uintptr_t>(d_b)) & 15) == 0;
+  if (al)
+    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch,
+                                                            d_done_flag);
+  else
+    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch,
+                                                                   d_done_flag);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_cg_init_state(double* d_state, const double* d_rr, double rtol, int32_t kmax, void* stream)
+{
+  B200_REQUIRE(d_state && d_rr, "NULL pointer");
+  if (int rc = need_gpu())
+    return rc;
+  init_state_kernel<<<1, 1, 0, as_stream(stream)>>>(d_state, d_rr, rtol, kmax);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_cg_update_xr_f64(int32_t n, double* d_state, const double* d_p, const double* d_Ap,
+                          double* d_x, double* d_r, void* stream)
+{
+  B200_REQUIRE(n >= 0 && d_state, "bad argument");
+  B200_REQUIRE(n == 0 || (d_p && d_Ap && d_x && d_r), "NULL vector");
+  if (int rc = need_gpu())
+    return rc;
+  update_xr_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_p, d_Ap, d_x,
+                                                                       d_r);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* d_p, double* d_hist,
+                         int32_t hist_len, void* stream)
+{
+  B200_REQUIRE(n >= 0 && d_state, "bad argument");
+  B200_REQUIRE(n == 0 || (d_r && d_p), "NULL vector");
+  if (int rc = need_gpu())
+    return rc;
+  update_p_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_r, d_p, d_hist,
+                                                                      hist_len);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,147 @@
+// common.cuh -- shared helpers for the sm_100a kernels behind include/b200spmv.h
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "b200spmv.h"
+
+namespace b200
+{
+
+// Thread-local error text behind b200_last_error().
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t err, const char* what, const char* file, int line);
+
+#define B200_CUDA(call)                                                        \
+  do {                                                                         \
+    cudaError_t err__ = (call);                                                \
+    if (err__ != cudaSuccess)                                                  \
+      return ::b200::cuda_fail(err__, #call, __FILE__, __LINE__);              \
+  } while (0)
+
+#define B200_LAUNCH_CHECK()                                                    \
+  do {                                                                         \
+    cudaError_t err__ = cudaGetLastError();                                    \
+    if (err__ != cudaSuccess)                                                  \
+      return ::b200::cuda_fail(err__, "kernel launch", __FILE__, __LINE__);    \
+  } while (0)
+
+#define B200_REQUIRE(cond, msg)                                                \
+  do {                                                                         \
+    if (!(cond)) {                                                             \
+      ::b200::set_error("%s (%s:%d)", msg, __FILE__, __LINE__);                \
+      return B200_EINVAL;                                                      \
+    }                                                                          \
+  } while (0)
+
+inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
+
+int num_sms(); // of the current device, cached
+
+// ---------------------------------------------------------------------------
+// SpMV plan (the `_aux_data` of csr_kernels.h:82).
+//
+// Rows are cut into tiles of roughly `tile_bytes` of matrix stream
+// (12 B per stored entry + 4 B per row).  tile_meta[2b] = first row of tile b,
+// tile_meta[2b+1] = rowptr[first row]; entry num_tiles is the end sentinel
+// {rows, nnz}.  A tile whose stream fits the stage buffer is staged in shared
+// memory by bulk-async copies and walked one thread per row; longer rows in it
+// are walked by a warp.  A tile that does not fit (one very long row) is read
+// straight from global memory, one warp per row.
+// ---------------------------------------------------------------------------
+struct Plan {
+  int32_t rows = 0;
+  int32_t cols = 0;
+  int64_t nnz = 0;
+  int symmetric = 0;
+  int variant = 0;
+  int32_t num_tiles = 0;
+  int32_t tile_bytes = 0;   // target bytes of matrix stream per tile
+  int32_t stage_bytes = 0;  // shared-memory stage size (tile_bytes + slack)
+  int32_t stages = 0;       // pipeline depth
+  int32_t consumer_warps = 0;
+  int32_t ctas_per_sm = 0;
+  int32_t* d_tile_meta = nullptr; // 2*(num_tiles+1) ints
+  int32_t max_row_len = 0;
+  int64_t hist[32] = {0};
+  double* d_partials = nullptr;    // dot epilogue: one partial per CTA
+  unsigned int* d_counter = nullptr; // last-CTA-done ticket
+  int32_t partials_len = 0;
+};
+
+// ---------------------------------------------------------------------------
+// PTX wrappers: mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "WAIT_%=:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+               "@p bra DONE_%=;\n"
+               "bra WAIT_%=;\n"
+               "DONE_%=:\n"
+               "}" ::"r"(smem_u32(bar)),
+               "r"(parity)
+               : "memory");
+}
+// Global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], "
+               "%2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads)
+{
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Arithmetic that is never contracted into FMA: the one-thread-per-row walk
+// then reproduces csr_kernels.cpp:41-51 (built for baseline x86-64, no FMA) bit
+// for bit.
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Fire-and-forget global add (SASS RED.E.ADD.F64 / .F32).
+__device__ __forceinline__ void red_add(double* addr, double v) { atomicAdd(addr, v); }
+__device__ __forceinline__ void red_add(float* addr, float v) { atomicAdd(addr, v); }
+
+} // namespace b200

@@ -1,0 +1,210 @@
+// runtime.cu -- memory / stream / event entry points of include/b200spmv.h.
+// Replaces the body of the reference's CudaExecutor (cuda/cuda_executor.cpp:
+// 54-105): cudaMalloc / cudaFree / cudaMemset / cudaMemcpy on one settable
+// stream, without the per-call device synchronisations.
+#include "common.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+namespace b200
+{
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t err, const char* what, const char* file, int line)
+{
+  set_error("CUDA error %d (%s) in %s at %s:%d", (int)err, cudaGetErrorString(err), what, file,
+            line);
+  return err == cudaErrorMemoryAllocation ? B200_ENOMEM : B200_ECUDA;
+}
+
+int num_sms()
+{
+  static thread_local int cached_dev = -1;
+  static thread_local int cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess)
+    return 0;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      return 0;
+    cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+const char* b200_last_error(void) { return g_err; }
+int b200_abi_version(void) { return 1; }
+
+int b200_device_count(int* count)
+{
+  B200_REQUIRE(count != nullptr, "count is NULL");
+  *count = 0;
+  B200_CUDA(cudaGetDeviceCount(count));
+  return B200_OK;
+}
+
+int b200_set_device(int device_id)
+{
+  B200_CUDA(cudaSetDevice(device_id));
+  return B200_OK;
+}
+
+int b200_get_num_sms(int* n)
+{
+  B200_REQUIRE(n != nullptr, "num_sms is NULL");
+  *n = num_sms();
+  if (*n <= 0) {
+    set_error("no CUDA device available");
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
+int b200_malloc(void** d_ptr, size_t num_bytes)
+{
+  B200_REQUIRE(d_ptr != nullptr, "d_ptr is NULL");
+  *d_ptr = nullptr;
+  if (num_bytes == 0)
+    return B200_OK;
+  B200_CUDA(cudaMalloc(d_ptr, num_bytes));
+  return B200_OK;
+}
+
+int b200_free(void* d_ptr)
+{
+  if (d_ptr != nullptr)
+    B200_CUDA(cudaFree(d_ptr));
+  return B200_OK;
+}
+
+int b200_memset_async(void* d_ptr, int value, size_t num_bytes, void* stream)
+{
+  if (num_bytes > 0)
+    B200_CUDA(cudaMemsetAsync(d_ptr, value, num_bytes, as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_memcpy_d2d_async(void* d_dst, const void* d_src, size_t num_bytes, void* stream)
+{
+  if (num_bytes > 0 && d_dst != d_src)
+    B200_CUDA(cudaMemcpyAsync(d_dst, d_src, num_bytes, cudaMemcpyDeviceToDevice,
+                              as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_memcpy_h2d_async(void* d_dst, const void* h_src, size_t num_bytes, void* stream)
+{
+  if (num_bytes > 0)
+    B200_CUDA(cudaMemcpyAsync(d_dst, h_src, num_bytes, cudaMemcpyHostToDevice,
+                              as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_memcpy_d2h_async(void* h_dst, const void* d_src, size_t num_bytes, void* stream)
+{
+  if (num_bytes > 0)
+    B200_CUDA(cudaMemcpyAsync(h_dst, d_src, num_bytes, cudaMemcpyDeviceToHost,
+                              as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_host_alloc_pinned(void** h_ptr, size_t num_bytes)
+{
+  B200_REQUIRE(h_ptr != nullptr, "h_ptr is NULL");
+  *h_ptr = nullptr;
+  if (num_bytes == 0)
+    return B200_OK;
+  B200_CUDA(cudaMallocHost(h_ptr, num_bytes));
+  return B200_OK;
+}
+
+int b200_host_free_pinned(void* h_ptr)
+{
+  if (h_ptr != nullptr)
+    B200_CUDA(cudaFreeHost(h_ptr));
+  return B200_OK;
+}
+
+int b200_stream_create(void** stream)
+{
+  B200_REQUIRE(stream != nullptr, "stream is NULL");
+  cudaStream_t s;
+  B200_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  *stream = s;
+  return B200_OK;
+}
+
+int b200_stream_destroy(void* stream)
+{
+  if (stream != nullptr)
+    B200_CUDA(cudaStreamDestroy(as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_stream_synchronize(void* stream)
+{
+  B200_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_event_create(void** event, int timing)
+{
+  B200_REQUIRE(event != nullptr, "event is NULL");
+  cudaEvent_t e;
+  B200_CUDA(cudaEventCreateWithFlags(&e, timing ? cudaEventDefault : cudaEventDisableTiming));
+  *event = e;
+  return B200_OK;
+}
+
+int b200_event_destroy(void* event)
+{
+  if (event != nullptr)
+    B200_CUDA(cudaEventDestroy(static_cast<cudaEvent_t>(event)));
+  return B200_OK;
+}
+
+int b200_event_record(void* event, void* stream)
+{
+  B200_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(event), as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_event_synchronize(void* event)
+{
+  B200_CUDA(cudaEventSynchronize(static_cast<cudaEvent_t>(event)));
+  return B200_OK;
+}
+
+int b200_stream_wait_event(void* stream, void* event)
+{
+  B200_CUDA(cudaStreamWaitEvent(as_stream(stream), static_cast<cudaEvent_t>(event), 0));
+  return B200_OK;
+}
+
+int b200_event_elapsed_ms(void* start, void* stop, float* ms)
+{
+  B200_REQUIRE(ms != nullptr, "ms is NULL");
+  B200_CUDA(cudaEventElapsedTime(ms, static_cast<cudaEvent_t>(start),
+                                 static_cast<cudaEvent_t>(stop)));
+  return B200_OK;
+}
+
+} // extern "C"

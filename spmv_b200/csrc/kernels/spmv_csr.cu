@@ -1,0 +1,839 @@
+// spmv_csr.cu -- fp64/fp32 CSR SpMV for sm_100a, general and symmetric storage.
+//
+// Replaces, behind CSRSpMV<T>::{init,run,finalize} (csr_kernels.h:71-78):
+//   general   : cusparseSpMV              (cuda/csr_kernels.cuda.cu:106-151)
+//   symmetric : csr_sym_gmem_atomics<T>   (cuda/csr_kernels.cuda.cu:22-47)
+// Arithmetic contract: csr_kernels.cpp:20-52.
+//
+// Design (HBM-bound streaming kernel, no tensor cores):
+//   * the plan cuts the rows into tiles of ~tile_bytes of matrix stream
+//     (values 8 B + colind 4 B per entry, rowptr 4 B per row);
+//   * a persistent CTA per SM slot owns tiles b, b+grid, ...; one producer lane
+//     streams each tile's values / colind / rowptr slices into a shared-memory
+//     ring with 1-D bulk-async copies (cp.async.bulk -> UBLKCP, completion on an
+//     mbarrier), `stages` deep, so HBM requests stay in flight while the consumer
+//     warps walk the previous tile;
+//   * consumers walk one thread per row out of shared memory, in the reference's
+//     j-ascending order with un-contracted mul/add (bit-identical to the CPU
+//     kernel when the row is short); lanes of a warp hold consecutive rows, so
+//     for banded / stencil matrices the x gathers coalesce and hit L1;
+//   * rows longer than 32 entries are walked by a whole warp afterwards; a tile
+//     that does not fit a stage (one huge row) is read directly from global
+//     memory one warp per row;
+//   * symmetric storage: the transpose contribution goes out as fire-and-forget
+//     RED.ADD.F64 (coalesced across the warp because lanes hold consecutive
+//     rows); y is pre-scaled by beta (or zeroed) because every write is an add.
+#include "common.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <new>
+#include <type_traits>
+
+namespace b200
+{
+
+constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
+constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
+constexpr int MAX_STAGE_BYTES = 96 * 1024;
+
+struct StageMeta {
+  int r0;
+  int nrows;
+  int lo;
+  int hi;
+  int fits;
+  int nlong;
+  int pad[2];
+  int long_rows[LONG_CAP];
+};
+
+template <typename T>
+struct SpmvArgs {
+  const int32_t* rowptr;
+  const int32_t* colind;
+  const T* val;
+  const T* diag;
+  const T* x;
+  T* y;
+  T alpha;
+  T beta;
+  const int32_t* tile_meta;
+  int32_t num_tiles;
+  int32_t stage_bytes;
+  int32_t stages;
+  double* partials;
+  unsigned int* counter;
+  double* dot_out;
+};
+
+__host__ __device__ __forceinline__ int round16(int b) { return (b + 15) & ~15; }
+
+// Byte layout of one staged tile: [values | colind | rowptr], each slice starting
+// at the 16-byte aligned global element at or below the tile's first element.
+template <typename T>
+struct TileLayout {
+  int lo_v, lo_c, lo_r;
+  int bytes_v, bytes_c, bytes_r;
+  __host__ __device__ TileLayout(int r0, int nrows, int lo, int hi)
+  {
+    constexpr int VA = 16 / (int)sizeof(T);
+    lo_v = lo & ~(VA - 1);
+    lo_c = lo & ~3;
+    lo_r = r0 & ~3;
+    bytes_v = round16((hi - lo_v) * (int)sizeof(T));
+    bytes_c = round16((hi - lo_c) * 4);
+    bytes_r = round16((r0 + nrows + 1 - lo_r) * 4);
+  }
+  __host__ __device__ int total() const { return bytes_v + bytes_c + bytes_r; }
+};
+
+// 64-bit pre-check first: a tile holding one enormous row must not overflow the
+// int byte counts of TileLayout.
+template <typename T>
+__host__ __device__ __forceinline__ bool tile_fits(int r0, int nrows, int lo, int hi, int sb)
+{
+  if ((long long)(hi - lo) * (long long)(sizeof(T) + 4) + 4ll * nrows > (long long)sb)
+    return false;
+  return TileLayout<T>(r0, nrows, lo, hi).total() <= sb;
+}
+
+// ---------------------------------------------------------------------------
+// Row walks
+// ---------------------------------------------------------------------------
+
+// One warp, one row, entries [rs, re) addressed through `col_at` / `val_at`.
+template <typename T, bool SYM, typename ColAt, typename ValAt>
+__device__ __forceinline__ T warp_row(const SpmvArgs<T>& a, int r, int rs, int re, int lane,
+                                      ColAt col_at, ValAt val_at)
+{
+  T xi = 0;
+  if (SYM)
+    xi = __ldg(a.x + r);
+  T part = 0;
+  for (int j = rs + lane; j < re; j += 32) {
+    const int c = col_at(j);
+    const T v = val_at(j);
+    part = fma(v, __ldg(a.x + c), part);
+    if (SYM)
+      red_add(a.y + c, a.alpha * v * xi);
+  }
+  part = warp_sum(part);
+  if (SYM)
+    part += __ldg(a.diag + r) * xi;
+  return part;
+}
+
+template <typename T, bool SYM>
+__device__ __forceinline__ T store_row(const SpmvArgs<T>& a, int r, T sum)
+{
+  T out = mul_rn(a.alpha, sum);
+  if (SYM) {
+    red_add(a.y + r, out);
+  } else {
+    if (a.beta != T(0))
+      out = add_rn(out, mul_rn(a.beta, a.y[r]));
+    a.y[r] = out;
+  }
+  return out;
+}
+
+// Walk a tile that sits in shared memory.  Returns this thread's share of
+// sum_i x[i]*y[i] over the tile's rows (general storage only).
+template <typename T, bool SYM, bool LONG, bool DOT>
+__device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsigned char* stage,
+                                              StageMeta* m, int tid, int nthreads, int warp,
+                                              int nwarps, int lane, int bar_id)
+{
+  const int r0 = m->r0, nrows = m->nrows, lo = m->lo, hi = m->hi;
+  const TileLayout<T> L(r0, nrows, lo, hi);
+  const T* sv = reinterpret_cast<const T*>(stage);
+  const int* sc = reinterpret_cast<const int*>(stage + L.bytes_v);
+  const int* sr = reinterpret_cast<const int*>(stage + L.bytes_v + L.bytes_c);
+  double dot = 0.0;
+
+  for (int k = tid; k < nrows; k += nthreads) {
+    const int r = r0 + k;
+    const int rs = sr[r - L.lo_r];
+    const int re = sr[r + 1 - L.lo_r];
+    if (LONG && re - rs > SHORT_ROW) {
+      const int q = atomicAdd(&m->nlong, 1);
+      m->long_rows[q] = k;
+      continue;
+    }
+    T xi = 0, sum = 0;
+    if (SYM) {
+      xi = __ldg(a.x + r);
+      sum = mul_rn(__ldg(a.diag + r), xi);
+    }
+    int j = rs;
+    for (; j + 4 <= re; j += 4) {
+      const int c0 = sc[j - L.lo_c], c1 = sc[j + 1 - L.lo_c];
+      const int c2 = sc[j + 2 - L.lo_c], c3 = sc[j + 3 - L.lo_c];
+      const T v0 = sv[j - L.lo_v], v1 = sv[j + 1 - L.lo_v];
+      const T v2 = sv[j + 2 - L.lo_v], v3 = sv[j + 3 - L.lo_v];
+      const T x0 = __ldg(a.x + c0), x1 = __ldg(a.x + c1);
+      const T x2 = __ldg(a.x + c2), x3 = __ldg(a.x + c3);
+      sum = add_rn(sum, mul_rn(v0, x0));
+      sum = add_rn(sum, mul_rn(v1, x1));
+      sum = add_rn(sum, mul_rn(v2, x2));
+      sum = add_rn(sum, mul_rn(v3, x3));
+      if (SYM) {
+        red_add(a.y + c0, mul_rn(mul_rn(a.alpha, v0), xi));
+        red_add(a.y + c1, mul_rn(mul_rn(a.alpha, v1), xi));
+        red_add(a.y + c2, mul_rn(mul_rn(a.alpha, v2), xi));
+        red_add(a.y + c3, mul_rn(mul_rn(a.alpha, v3), xi));
+      }
+    }
+    for (; j < re; ++j) {
+      const int c = sc[j - L.lo_c];
+      const T v = sv[j - L.lo_v];
+      sum = add_rn(sum, mul_rn(v, __ldg(a.x + c)));
+      if (SYM)
+        red_add(a.y + c, mul_rn(mul_rn(a.alpha, v), xi));
+    }
+    const T out = store_row<T, SYM>(a, r, sum);
+    if (DOT)
+      dot += (double)__ldg(a.x + r) * (double)out;
+  }
+
+  if (LONG) {
+    named_bar_sync(bar_id, nthreads);
+    const int nlong = m->nlong;
+    for (int q = warp; q < nlong; q += nwarps) {
+      const int r = r0 + m->long_rows[q];
+      const int rs = sr[r - L.lo_r], re = sr[r + 1 - L.lo_r];
+      const T sum = warp_row<T, SYM>(
+          a, r, rs, re, lane, [&](int j) { return sc[j - L.lo_c]; },
+          [&](int j) { return sv[j - L.lo_v]; });
+      if (lane == 0) {
+        const T out = store_row<T, SYM>(a, r, sum);
+        if (DOT)
+          dot += (double)__ldg(a.x + r) * (double)out;
+      }
+    }
+  }
+  return dot;
+}
+
+// Walk a tile straight from global memory, one warp per row.
+template <typename T, bool SYM, bool DOT>
+__device__ __forceinline__ double walk_direct(const SpmvArgs<T>& a, int r0, int nrows, int warp,
+                                              int nwarps, int lane)
+{
+  double dot = 0.0;
+  for (int k = warp; k < nrows; k += nwarps) {
+    const int r = r0 + k;
+    const int rs = __ldg(a.rowptr + r), re = __ldg(a.rowptr + r + 1);
+    const T sum = warp_row<T, SYM>(
+        a, r, rs, re, lane, [&](int j) { return __ldg(a.colind + j); },
+        [&](int j) { return __ldg(a.val + j); });
+    if (lane == 0) {
+      const T out = store_row<T, SYM>(a, r, sum);
+      if (DOT)
+        dot += (double)__ldg(a.x + r) * (double)out;
+    }
+  }
+  return dot;
+}
+
+// Deterministic grid-wide sum of one double per thread of the first `nthreads`
+// threads: warp tree -> per-CTA partial -> last CTA folds the partials in a
+// fixed order.
+__device__ __forceinline__ void grid_dot_reduce(double v, int tid, int nthreads, int bar_id,
+                                                double* s_warp, double* partials,
+                                                unsigned int* counter, double* out)
+{
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
+  v = warp_sum(v);
+  if (lane == 0)
+    s_warp[warp] = v;
+  named_bar_sync(bar_id, nthreads);
+  if (warp == 0) {
+    double t = 0.0;
+    if (lane == 0) {
+      for (int w = 0; w < nwarps; ++w)
+        t += s_warp[w];
+      partials[blockIdx.x] = t;
+      __threadfence();
+    }
+    unsigned int ticket = 0;
+    if (lane == 0)
+      ticket = atomicAdd(counter, 1u);
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) {
+      __threadfence();
+      double s = 0.0;
+      for (int i = lane; i < (int)gridDim.x; i += 32)
+        s += __ldcg(partials + i);
+      s = warp_sum(s);
+      if (lane == 0) {
+        out[0] = s;
+        *counter = 0u;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Variant 0: persistent CTAs, bulk-async staged ring, warp-specialised.
+//   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
+// ---------------------------------------------------------------------------
+template <typename T, bool SYM, bool DOT, bool LONG, int CW>
+__global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
+{
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int stages = a.stages;
+  const int sb = a.stage_bytes;
+  StageMeta* meta = reinterpret_cast<StageMeta*>(smem + (size_t)stages * sb);
+  uint64_t* full = reinterpret_cast<uint64_t*>(meta + stages);
+  uint64_t* empty = full + stages;
+  double* s_warp = reinterpret_cast<double*>(empty + stages);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, CW);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int my_tiles
+      = ((int)blockIdx.x < a.num_tiles)
+            ? (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x
+            : 0;
+
+  if (warp == CW) {
+    if (lane == 0) {
+      for (int it = 0; it < my_tiles; ++it) {
+        const int s = it % stages, use = it / stages;
+        if (use > 0)
+          mbar_wait(empty + s, (use - 1) & 1);
+        const int tile = blockIdx.x + it * gridDim.x;
+        const int2 t0 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile);
+        const int2 t1 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile + 1);
+        const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x, hi = t1.y;
+        const int fits = tile_fits<T>(r0, nrows, lo, hi, sb);
+        StageMeta* m = meta + s;
+        m->r0 = r0;
+        m->nrows = nrows;
+        m->lo = lo;
+        m->hi = hi;
+        m->fits = fits;
+        m->nlong = 0;
+        if (fits) {
+          const TileLayout<T> L(r0, nrows, lo, hi);
+          unsigned char* dst = smem + (size_t)s * sb;
+          mbar_arrive_expect_tx(full + s, (uint32_t)L.total());
+          if (L.bytes_v > 0)
+            bulk_g2s(dst, a.val + L.lo_v, L.bytes_v, full + s);
+          if (L.bytes_c > 0)
+            bulk_g2s(dst + L.bytes_v, a.colind + L.lo_c, L.bytes_c, full + s);
+          bulk_g2s(dst + L.bytes_v + L.bytes_c, a.rowptr + L.lo_r, L.bytes_r, full + s);
+        } else {
+          mbar_arrive(full + s);
+        }
+      }
+    }
+    return;
+  }
+
+  double dot = 0.0;
+  for (int it = 0; it < my_tiles; ++it) {
+    const int s = it % stages, use = it / stages;
+    mbar_wait(full + s, use & 1);
+    StageMeta* m = meta + s;
+    if (m->fits)
+      dot += walk_staged<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp, CW,
+                                       lane, 1);
+    else
+      dot += walk_direct<T, SYM, DOT>(a, m->r0, m->nrows, warp, CW, lane);
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(empty + s);
+  }
+  if (DOT)
+    grid_dot_reduce(dot, threadIdx.x, CW * 32, 2, s_warp, a.partials, a.counter, a.dot_out);
+}
+
+// ---------------------------------------------------------------------------
+// Variant 1: one tile per CTA, staged with plain vector loads.  Used when a
+// base pointer is not 16-byte aligned, and as the comparison point for variant 0.
+// ---------------------------------------------------------------------------
+template <typename T, bool SYM, bool LONG, int NT>
+__global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
+{
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int sb = a.stage_bytes;
+  StageMeta* m = reinterpret_cast<StageMeta*>(smem + sb);
+  const int tile = blockIdx.x;
+  const int r0 = __ldg(a.tile_meta + 2 * tile), lo = __ldg(a.tile_meta + 2 * tile + 1);
+  const int r1 = __ldg(a.tile_meta + 2 * tile + 2), hi = __ldg(a.tile_meta + 2 * tile + 3);
+  const int nrows = r1 - r0;
+  if (nrows == 0)
+    return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (!tile_fits<T>(r0, nrows, lo, hi, sb)) {
+    walk_direct<T, SYM, false>(a, r0, nrows, warp, NT / 32, lane);
+    return;
+  }
+  const TileLayout<T> L(r0, nrows, lo, hi);
+  if (threadIdx.x == 0) {
+    m->r0 = r0;
+    m->nrows = nrows;
+    m->lo = lo;
+    m->hi = hi;
+    m->fits = 1;
+    m->nlong = 0;
+  }
+  T* sv = reinterpret_cast<T*>(smem);
+  int* sc = reinterpret_cast<int*>(smem + L.bytes_v);
+  int* sr = reinterpret_cast<int*>(smem + L.bytes_v + L.bytes_c);
+  for (int j = lo + threadIdx.x; j < hi; j += NT)
+    sv[j - L.lo_v] = __ldg(a.val + j);
+  for (int j = lo + threadIdx.x; j < hi; j += NT)
+    sc[j - L.lo_c] = __ldg(a.colind + j);
+  for (int r = r0 + threadIdx.x; r <= r1; r += NT)
+    sr[r - L.lo_r] = __ldg(a.rowptr + r);
+  __syncthreads();
+  walk_staged<T, SYM, LONG, false>(a, smem, m, threadIdx.x, NT, warp, NT / 32, lane, 1);
+}
+
+// Diagonal-only symmetric block (nnz == 0, rowptr == NULL): csr_matrix.cpp:85,
+// openmp/csr_kernels.openmp.cpp:222-225.
+template <typename T>
+__global__ void diag_only_kernel(int n, const T* __restrict__ diag, const T* __restrict__ x, T alpha,
+                                 T beta, T* __restrict__ y)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    T out = mul_rn(alpha, mul_rn(diag[i], x[i]));
+    if (beta != T(0))
+      out = add_rn(out, mul_rn(beta, y[i]));
+    y[i] = out;
+  }
+}
+
+template <typename T>
+__global__ void scale_kernel(int n, T beta, T* __restrict__ y)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    y[i] = mul_rn(beta, y[i]);
+}
+
+// ---------------------------------------------------------------------------
+// Plan kernels
+// ---------------------------------------------------------------------------
+__global__ void plan_tiles_kernel(const int32_t* __restrict__ rowptr, int rows, long long nnz,
+                                  int num_tiles, long long tile_bytes, int32_t* __restrict__ meta)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > num_tiles)
+    return;
+  if (b == num_tiles) {
+    meta[2 * b] = rows;
+    meta[2 * b + 1] = (int32_t)nnz;
+    return;
+  }
+  const long long target = (long long)b * tile_bytes;
+  int lo = 0, hi = rows; // smallest r with 12*rowptr[r] + 4*r >= target
+  while (lo < hi) {
+    const int mid = lo + ((hi - lo) >> 1);
+    const long long g = 12ll * rowptr[mid] + 4ll * mid;
+    if (g >= target)
+      hi = mid;
+    else
+      lo = mid + 1;
+  }
+  meta[2 * b] = lo;
+  meta[2 * b + 1] = rowptr[lo];
+}
+
+__global__ void plan_hist_kernel(const int32_t* __restrict__ rowptr, int rows,
+                                 unsigned long long* __restrict__ hist, int* __restrict__ max_len)
+{
+  __shared__ unsigned int s_hist[32];
+  __shared__ int s_max;
+  if (threadIdx.x < 32)
+    s_hist[threadIdx.x] = 0;
+  if (threadIdx.x == 0)
+    s_max = 0;
+  __syncthreads();
+  int local_max = 0;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+    const int len = rowptr[r + 1] - rowptr[r];
+    const int bucket = len <= 0 ? 0 : 32 - __clz(len);
+    atomicAdd(&s_hist[bucket > 31 ? 31 : bucket], 1u);
+    local_max = max(local_max, len);
+  }
+  atomicMax(&s_max, local_max);
+  __syncthreads();
+  if (threadIdx.x < 32 && s_hist[threadIdx.x] > 0)
+    atomicAdd(&hist[threadIdx.x], (unsigned long long)s_hist[threadIdx.x]);
+  if (threadIdx.x == 0)
+    atomicMax(max_len, s_max);
+}
+
+static int env_int(const char* name, int dflt)
+{
+  const char* v = std::getenv(name);
+  return (v && *v) ? std::atoi(v) : dflt;
+}
+
+static size_t pipe_smem_bytes(const Plan& p)
+{
+  return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 16 * p.stages + 8 * 32;
+}
+
+static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
+{
+  if (p->d_tile_meta) {
+    B200_CUDA(cudaFree(p->d_tile_meta));
+    p->d_tile_meta = nullptr;
+  }
+  p->num_tiles = 0;
+  if (p->nnz == 0 || p->rows == 0 || d_rowptr == nullptr)
+    return B200_OK;
+  const long long total = 12ll * p->nnz + 4ll * p->rows;
+  const long long nt = (total + p->tile_bytes - 1) / p->tile_bytes;
+  B200_REQUIRE(nt < (1ll << 30), "too many tiles");
+  p->num_tiles = (int32_t)nt;
+  B200_CUDA(cudaMalloc(&p->d_tile_meta, sizeof(int32_t) * 2 * (size_t)(nt + 1)));
+  const int threads = 256;
+  const int blocks = (int)((nt + 1 + threads - 1) / threads);
+  plan_tiles_kernel<<<blocks, threads, 0, st>>>(d_rowptr, p->rows, p->nnz, p->num_tiles,
+                                                p->tile_bytes, p->d_tile_meta);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
+{
+  B200_REQUIRE(variant == 0 || variant == 1, "variant must be 0 or 1");
+  B200_REQUIRE(tile_bytes >= 1024 && tile_bytes + 2048 <= MAX_STAGE_BYTES, "tile_bytes out of range");
+  B200_REQUIRE(stages >= 2 && stages <= 8, "stages out of range");
+  B200_REQUIRE(cw == 2 || cw == 4 || cw == 8, "consumer_warps must be 2, 4 or 8");
+  B200_REQUIRE(ctas >= 1 && ctas <= 8, "ctas_per_sm out of range");
+  p->variant = variant;
+  p->tile_bytes = tile_bytes;
+  p->stage_bytes = tile_bytes + 2048; // slack: one row of up to ~160 entries
+  p->stages = stages;
+  p->consumer_warps = cw;
+  p->ctas_per_sm = ctas;
+  B200_REQUIRE(pipe_smem_bytes(*p) <= 227 * 1024, "stages * stage_bytes exceeds shared memory");
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Launch
+// ---------------------------------------------------------------------------
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device: cache per device.
+struct SmemCache {
+  size_t configured[64] = {0};
+};
+
+template <typename Kernel>
+static int set_smem(Kernel k, size_t bytes, SmemCache& cache)
+{
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || cache.configured[dev] < bytes) {
+    B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    if (dev >= 0 && dev < 64)
+      cache.configured[dev] = bytes;
+  }
+  return B200_OK;
+}
+
+template <typename T, bool SYM, bool DOT, bool LONG, int CW>
+static int launch_pipe(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
+{
+  const size_t smem = pipe_smem_bytes(p);
+  static SmemCache cache;
+  if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW>, smem, cache))
+    return rc;
+  const int grid = std::min<long long>(p.num_tiles, (long long)num_sms() * p.ctas_per_sm);
+  spmv_pipe_kernel<T, SYM, DOT, LONG, CW><<<grid, (CW + 1) * 32, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+template <typename T, bool SYM, bool DOT, bool LONG>
+static int launch_pipe_cw(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
+{
+  switch (p.consumer_warps) {
+  case 2:
+    return launch_pipe<T, SYM, DOT, LONG, 2>(p, a, st);
+  case 4:
+    return launch_pipe<T, SYM, DOT, LONG, 4>(p, a, st);
+  default:
+    return launch_pipe<T, SYM, DOT, LONG, 8>(p, a, st);
+  }
+}
+
+template <typename T, bool SYM, bool LONG>
+static int launch_tile(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
+{
+  constexpr int NT = 256;
+  const size_t smem = p.stage_bytes + sizeof(StageMeta);
+  static SmemCache cache;
+  if (int rc = set_smem(spmv_tile_kernel<T, SYM, LONG, NT>, smem, cache))
+    return rc;
+  spmv_tile_kernel<T, SYM, LONG, NT><<<p.num_tiles, NT, smem, st>>>(a);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename T, bool SYM>
+static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_colind, const T* d_val,
+                    const T* d_diag, T alpha, const T* d_x, T beta, T* d_y, double* d_dot,
+                    void* stream)
+{
+  B200_REQUIRE(plan_v != nullptr, "plan is NULL");
+  const Plan& p = *static_cast<const Plan*>(plan_v);
+  B200_REQUIRE(SYM == (p.symmetric != 0), "plan / call symmetric mismatch");
+  B200_REQUIRE(p.rows == 0 || (d_x != nullptr && d_y != nullptr), "x or y is NULL");
+  if (num_sms() <= 0) {
+    set_error("no CUDA device available: this build has no CPU path");
+    return B200_ECUDA;
+  }
+  cudaStream_t st = as_stream(stream);
+  if (p.rows == 0)
+    return B200_OK;
+  const int tb = 256, gb = (p.rows + tb - 1) / tb;
+
+  if (SYM) {
+    B200_REQUIRE(d_diag != nullptr, "symmetric SpMV needs the diagonal");
+    if (p.num_tiles == 0) {
+      diag_only_kernel<T><<<gb, tb, 0, st>>>(p.rows, d_diag, d_x, alpha, beta, d_y);
+      B200_LAUNCH_CHECK();
+      return B200_OK;
+    }
+    // every write below is an add: bring y to beta*y first
+    if (beta == T(0))
+      B200_CUDA(cudaMemsetAsync(d_y, 0, sizeof(T) * (size_t)p.rows, st));
+    else if (beta != T(1)) {
+      scale_kernel<T><<<gb, tb, 0, st>>>(p.rows, beta, d_y);
+      B200_LAUNCH_CHECK();
+    }
+  } else if (p.num_tiles == 0) {
+    // empty block: y = beta*y
+    if (beta == T(0))
+      B200_CUDA(cudaMemsetAsync(d_y, 0, sizeof(T) * (size_t)p.rows, st));
+    else if (beta != T(1)) {
+      scale_kernel<T><<<gb, tb, 0, st>>>(p.rows, beta, d_y);
+      B200_LAUNCH_CHECK();
+    }
+    if (d_dot)
+      B200_CUDA(cudaMemsetAsync(d_dot, 0, sizeof(double), st));
+    return B200_OK;
+  }
+  B200_REQUIRE(d_rowptr && d_colind && d_val, "matrix arrays are NULL but nnz > 0");
+
+  SpmvArgs<T> a;
+  a.rowptr = d_rowptr;
+  a.colind = d_colind;
+  a.val = d_val;
+  a.diag = d_diag;
+  a.x = d_x;
+  a.y = d_y;
+  a.alpha = alpha;
+  a.beta = beta;
+  a.tile_meta = p.d_tile_meta;
+  a.num_tiles = p.num_tiles;
+  a.stage_bytes = p.stage_bytes;
+  a.stages = p.stages;
+  a.partials = p.d_partials;
+  a.counter = p.d_counter;
+  a.dot_out = d_dot;
+
+  const bool has_long = p.max_row_len > SHORT_ROW;
+  const bool bulk_ok = aligned16(d_rowptr) && aligned16(d_colind) && aligned16(d_val);
+  if (p.variant == 0 && bulk_ok) {
+    if (d_dot != nullptr) {
+      B200_REQUIRE((std::is_same<T, double>::value) && !SYM, "dot epilogue: general fp64 only");
+      B200_REQUIRE((long long)num_sms() * p.ctas_per_sm <= p.partials_len, "partials too small");
+      if (has_long)
+        return launch_pipe_cw<T, SYM, !SYM, true>(p, a, st);
+      return launch_pipe_cw<T, SYM, !SYM, false>(p, a, st);
+    }
+    if (has_long)
+      return launch_pipe_cw<T, SYM, false, true>(p, a, st);
+    return launch_pipe_cw<T, SYM, false, false>(p, a, st);
+  }
+  B200_REQUIRE(d_dot == nullptr, "dot epilogue needs variant 0 and 16-byte aligned arrays");
+  if (has_long)
+    return launch_tile<T, SYM, true>(p, a, st);
+  return launch_tile<T, SYM, false>(p, a, st);
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
+                         const int32_t* d_rowptr, int symmetric, void* stream)
+{
+  B200_REQUIRE(plan != nullptr, "plan is NULL");
+  *plan = nullptr;
+  B200_REQUIRE(rows >= 0 && cols >= 0 && nnz >= 0, "negative size");
+  B200_REQUIRE(nnz < (1ll << 31), "nnz does not fit the int32 rowptr");
+  B200_REQUIRE(nnz == 0 || d_rowptr != nullptr, "rowptr is NULL but nnz > 0");
+  if (num_sms() <= 0) {
+    set_error("no CUDA device available: this build has no CPU path");
+    return B200_ECUDA;
+  }
+  Plan* p = new (std::nothrow) Plan();
+  if (!p)
+    return B200_ENOMEM;
+  p->rows = rows;
+  p->cols = cols;
+  p->nnz = nnz;
+  p->symmetric = symmetric ? 1 : 0;
+  int rc = plan_apply_tuning(p, env_int("B200_SPMV_VARIANT", 0),
+                             env_int("B200_SPMV_TILE_BYTES", 32 * 1024),
+                             env_int("B200_SPMV_STAGES", 3), env_int("B200_SPMV_CWARPS", 4),
+                             env_int("B200_SPMV_CTAS", 2));
+  if (rc) {
+    delete p;
+    return rc;
+  }
+  cudaStream_t st = as_stream(stream);
+  rc = plan_partition(p, d_rowptr, st);
+  if (rc) {
+    b200_csr_plan_destroy(p);
+    return rc;
+  }
+  p->partials_len = num_sms() * 8;
+  unsigned long long* d_hist = nullptr;
+  int* d_max = nullptr;
+  auto fail = [&](int code) {
+    cudaFree(d_hist);
+    cudaFree(d_max);
+    b200_csr_plan_destroy(p);
+    return code;
+  };
+  if (cudaMalloc(&p->d_partials, sizeof(double) * p->partials_len) != cudaSuccess
+      || cudaMalloc(&p->d_counter, sizeof(unsigned int)) != cudaSuccess
+      || cudaMalloc(&d_hist, sizeof(unsigned long long) * 32) != cudaSuccess
+      || cudaMalloc(&d_max, sizeof(int)) != cudaSuccess) {
+    set_error("cudaMalloc failed in plan_create");
+    return fail(B200_ENOMEM);
+  }
+  cudaMemsetAsync(p->d_counter, 0, sizeof(unsigned int), st);
+  cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * 32, st);
+  cudaMemsetAsync(d_max, 0, sizeof(int), st);
+  if (p->num_tiles > 0) {
+    const int blocks = std::min((rows + 255) / 256, num_sms() * 8);
+    plan_hist_kernel<<<blocks, 256, 0, st>>>(d_rowptr, rows, d_hist, d_max);
+  }
+  unsigned long long h[32];
+  int mx = 0;
+  if (cudaMemcpyAsync(h, d_hist, sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess
+      || cudaMemcpyAsync(&mx, d_max, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess
+      || cudaStreamSynchronize(st) != cudaSuccess) {
+    cuda_fail(cudaGetLastError(), "plan_create readback", __FILE__, __LINE__);
+    return fail(B200_ECUDA);
+  }
+  for (int i = 0; i < 32; ++i)
+    p->hist[i] = (int64_t)h[i];
+  p->max_row_len = mx;
+  cudaFree(d_hist);
+  cudaFree(d_max);
+  *plan = p;
+  return B200_OK;
+}
+
+int b200_csr_plan_destroy(void* plan)
+{
+  Plan* p = static_cast<Plan*>(plan);
+  if (!p)
+    return B200_OK;
+  cudaFree(p->d_tile_meta);
+  cudaFree(p->d_partials);
+  cudaFree(p->d_counter);
+  delete p;
+  return B200_OK;
+}
+
+int b200_csr_plan_info(void* plan, int32_t* num_tiles, int32_t* max_row_len, int64_t hist[32])
+{
+  B200_REQUIRE(plan != nullptr, "plan is NULL");
+  const Plan* p = static_cast<const Plan*>(plan);
+  if (num_tiles)
+    *num_tiles = p->num_tiles;
+  if (max_row_len)
+    *max_row_len = p->max_row_len;
+  if (hist)
+    for (int i = 0; i < 32; ++i)
+      hist[i] = p->hist[i];
+  return B200_OK;
+}
+
+int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int tile_bytes,
+                       int stages, int consumer_warps, int ctas_per_sm, void* stream)
+{
+  B200_REQUIRE(plan != nullptr, "plan is NULL");
+  Plan* p = static_cast<Plan*>(plan);
+  const int old_tile = p->tile_bytes;
+  int rc = plan_apply_tuning(p, variant, tile_bytes, stages, consumer_warps, ctas_per_sm);
+  if (rc)
+    return rc;
+  if (tile_bytes != old_tile) {
+    rc = plan_partition(p, d_rowptr, as_stream(stream));
+    if (rc)
+      return rc;
+    B200_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  }
+  return B200_OK;
+}
+
+int b200_csr_spmv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const double* d_val, double alpha, const double* d_x, double beta,
+                      double* d_y, void* stream)
+{
+  return run_spmv<double, false>(plan, d_rowptr, d_colind, d_val, nullptr, alpha, d_x, beta, d_y,
+                                 nullptr, stream);
+}
+
+int b200_csr_spmv_f32(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const float* d_val, float alpha, const float* d_x, float beta, float* d_y,
+                      void* stream)
+{
+  return run_spmv<float, false>(plan, d_rowptr, d_colind, d_val, nullptr, alpha, d_x, beta, d_y,
+                                nullptr, stream);
+}
+
+int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                          const double* d_val, const double* d_x, double* d_y, double* d_dot,
+                          void* stream)
+{
+  B200_REQUIRE(d_dot != nullptr, "d_dot is NULL");
+  return run_spmv<double, false>(plan, d_rowptr, d_colind, d_val, nullptr, 1.0, d_x, 0.0, d_y,
+                                 d_dot, stream);
+}
+
+int b200_csr_symv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const double* d_val, const double* d_diag, double alpha, const double* d_x,
+                      double beta, double* d_y, void* stream)
+{
+  return run_spmv<double, true>(plan, d_rowptr, d_colind, d_val, d_diag, alpha, d_x, beta, d_y,
+                                nullptr, stream);
+}
+
+int b200_csr_symv_f32(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                      const float* d_val, const float* d_diag, float alpha, const float* d_x,
+                      float beta, float* d_y, void* stream)
+{
+  return run_spmv<float, true>(plan, d_rowptr, d_colind, d_val, d_diag, alpha, d_x, beta, d_y,
+                               nullptr, stream);
+}
+
+} // extern "C"

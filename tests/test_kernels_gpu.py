@@ -1,0 +1,358 @@
+"""GPU parity: every kernel behind include/b200spmv.h against the CPU oracle, through
+the C ABI, on the same seeded inputs.  Tolerances: y within 1e-12 relative L2
+(BASELINE.json); index work bit-exact; where the kernel walks one thread per row in
+the reference's order the result is also required to be bit-identical."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+from oracle import kernels as OK
+from spmv_b200 import kernels as K
+from spmv_b200 import synth
+from tests.fixtures import (FIX_COLIND, FIX_ROWPTR, FIX_SYM_COLIND, FIX_SYM_DIAG, FIX_SYM_ROWPTR, FIX_SYM_VALUES,
+                            FIX_VALUES, FIX_X, FIX_Y, rel_l2, split_symmetric)
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+VARIANTS = [
+    dict(variant=0, tile_bytes=32768, stages=3, consumer_warps=4, ctas_per_sm=2),
+    dict(variant=0, tile_bytes=4096, stages=2, consumer_warps=2, ctas_per_sm=4),
+    dict(variant=0, tile_bytes=65536, stages=3, consumer_warps=8, ctas_per_sm=1),
+    dict(variant=1, tile_bytes=16384, stages=2, consumer_warps=4, ctas_per_sm=2),
+]
+
+
+def dev_csr(rowptr, colind, values, dev, dtype=torch.float64):
+    return (torch.from_numpy(np.ascontiguousarray(rowptr, dtype=np.int32)).to(dev),
+            torch.from_numpy(np.ascontiguousarray(colind, dtype=np.int32)).to(dev),
+            torch.from_numpy(np.ascontiguousarray(values)).to(dev).to(dtype))
+
+
+def run_general(dev, rowptr, colind, values, x, ncols, alpha=1.0, beta=0.0, y0=None, tune=None, dtype=torch.float64):
+    rp, ci, v = dev_csr(rowptr, colind, values, dev, dtype)
+    n = len(rowptr) - 1
+    plan = K.CsrPlan(n, ncols, rp, False)
+    if tune:
+        plan.tune(**tune)
+    xd = torch.from_numpy(np.ascontiguousarray(x)).to(dev).to(dtype)
+    y = torch.full((n,), float("nan"), dtype=dtype, device=dev) if y0 is None else torch.from_numpy(y0).to(dev).to(dtype)
+    K.spmv(plan, rp, ci, v, xd, y, alpha, beta)
+    torch.cuda.synchronize()
+    info = plan.info()
+    plan.close()
+    return y.cpu().numpy(), info
+
+
+def run_sym(dev, rp, ci, v, d, x, alpha=1.0, beta=0.0, y0=None, tune=None, dtype=torch.float64):
+    n = len(d)
+    nnz = 0 if v is None else len(v)
+    if nnz:
+        rpd, cid, vd = dev_csr(rp, ci, v, dev, dtype)
+    else:
+        rpd = cid = vd = None
+    dd = torch.from_numpy(np.ascontiguousarray(d)).to(dev).to(dtype)
+    plan = K.CsrPlan(n, n, rpd, True, nnz=nnz)
+    if tune:
+        plan.tune(**tune)
+    xd = torch.from_numpy(np.ascontiguousarray(x)).to(dev).to(dtype)
+    y = torch.full((n,), float("nan"), dtype=dtype, device=dev) if y0 is None else torch.from_numpy(y0).to(dev).to(dtype)
+    K.symv(plan, rpd, cid, vd, dd, xd, y, alpha, beta)
+    torch.cuda.synchronize()
+    plan.close()
+    return y.cpu().numpy()
+
+
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_fixture_general(cuda, tune):
+    y, _ = run_general(cuda, FIX_ROWPTR, FIX_COLIND, FIX_VALUES, FIX_X, 5, tune=tune)
+    assert np.array_equal(y, FIX_Y)  # reference golden values, bit for bit
+
+
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_fixture_symmetric(cuda, tune):
+    y = run_sym(cuda, FIX_SYM_ROWPTR, FIX_SYM_COLIND, FIX_SYM_VALUES, FIX_SYM_DIAG, FIX_X, tune=tune)
+    assert rel_l2(y, FIX_Y) < TOL
+    assert abs(np.linalg.norm(y) - 1.3857542692681533) < 1e-15 * 4
+
+
+def test_diag_only_symmetric(cuda):
+    # rank 1 of the reference's 2-rank symmetric test: local block has no off-diagonals
+    x = np.array([0.5, -2.0])
+    y = run_sym(cuda, None, None, None, np.array([8.0, 8.0]), x)
+    assert np.array_equal(y, OK.symv(None, None, None, np.array([8.0, 8.0]), x))
+    y = run_sym(cuda, None, None, None, np.array([8.0, 8.0]), x, alpha=0.5, beta=2.0, y0=np.array([1.0, 1.0]))
+    assert np.array_equal(y, OK.symv(None, None, None, np.array([8.0, 8.0]), x, 0.5, 2.0, np.array([1.0, 1.0])))
+
+
+@pytest.mark.parametrize("stencil", [7, 27])
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_laplace_general_bit_exact(cuda, stencil, tune):
+    n1 = 20
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, stencil)
+    x = synth.bump_vector(N, 0, N) + 0.01 * np.random.default_rng(0).standard_normal(N)
+    y, info = run_general(cuda, rp, col, val, x, N, tune=tune)
+    want = OK.spmv(rp, col, val, x)
+    assert info["max_row_len"] == stencil
+    assert np.array_equal(y, want)  # thread-per-row walk, reference order, no FMA
+
+
+@pytest.mark.parametrize("alpha,beta", [(1.0, 1.0), (0.5, 0.0), (-2.0, 0.25)])
+def test_general_alpha_beta(cuda, alpha, beta):
+    rng = np.random.default_rng(1)
+    A = sp.random(3000, 3500, density=0.004, format="csr", random_state=4)
+    A.sort_indices()
+    x, y0 = rng.standard_normal(3500), rng.standard_normal(3000)
+    y, _ = run_general(cuda, A.indptr, A.indices, A.data, x, 3500, alpha, beta, y0.copy())
+    assert rel_l2(y, OK.spmv(A.indptr, A.indices, A.data, x, alpha, beta, y0)) < TOL
+
+
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_powerlaw_irregular(cuda, tune):
+    n = 60000
+    rp, col, val = synth.powerlaw_rows(n, 0, n, band=2048)
+    x = np.random.default_rng(2).standard_normal(n)
+    y, info = run_general(cuda, rp, col, val, x, n, tune=tune)
+    assert info["max_row_len"] > 64  # exercises the warp-per-row walk
+    assert sum(info["hist"]) == n
+    assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL
+
+
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_huge_row_and_empty_rows(cuda, tune):
+    # rows: empty, short, one row far larger than a stage (direct path), empty tail
+    rng = np.random.default_rng(3)
+    ncols = 200000
+    lens = np.array([0, 3, 0, 150000, 5, 0, 0, 40, 33, 32, 31, 0], dtype=np.int64)
+    lens = np.concatenate([lens, rng.integers(0, 12, size=500), [0, 0, 0]])
+    rp = np.zeros(len(lens) + 1, dtype=np.int64)
+    np.cumsum(lens, out=rp[1:])
+    col = np.concatenate([np.sort(rng.choice(ncols, size=l, replace=False)) for l in lens]).astype(np.int64)
+    val = rng.standard_normal(rp[-1])
+    x = rng.standard_normal(ncols)
+    y, info = run_general(cuda, rp, col, val, x, ncols, tune=tune)
+    assert info["hist"][0] == int((lens == 0).sum())
+    assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL
+
+
+def test_zero_rows_and_zero_nnz(cuda):
+    y, info = run_general(cuda, np.zeros(1, np.int32), np.zeros(0, np.int32), np.zeros(0), np.zeros(4), 4)
+    assert y.size == 0 and info["num_tiles"] == 0
+    # nnz == 0 with rows > 0: y = beta*y
+    rp = np.zeros(11, np.int32)
+    y, _ = run_general(cuda, rp, np.zeros(0, np.int32), np.zeros(0), np.ones(10), 10, 1.0, 2.0, np.arange(10.0))
+    assert np.array_equal(y, 2.0 * np.arange(10.0))
+    y, _ = run_general(cuda, rp, np.zeros(0, np.int32), np.zeros(0), np.ones(10), 10)
+    assert np.array_equal(y, np.zeros(10))
+
+
+@pytest.mark.parametrize("tune", VARIANTS)
+def test_laplace_symmetric(cuda, tune):
+    n1 = 24
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 7)
+    srp, sci, sv, d = split_symmetric(rp, col, val)
+    x = synth.bump_vector(N, 0, N)
+    y = run_sym(cuda, srp, sci, sv, d, x, tune=tune)
+    want = OK.symv(srp, sci, sv, d, x)
+    assert rel_l2(y, want) < TOL
+    assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL  # same operator as the full storage
+
+
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.5, 1.0), (-1.5, 0.25)])
+def test_random_symmetric(cuda, alpha, beta):
+    rng = np.random.default_rng(5)
+    n = 5000
+    rp0, col0, val0 = synth.powerlaw_rows(n, 0, n, band=512)
+    A = sp.csr_matrix((val0, col0, rp0), shape=(n, n))
+    S = (A + A.T).tocsr()
+    S.sort_indices()
+    srp, sci, sv, d = split_symmetric(S.indptr, S.indices, S.data)
+    x, y0 = rng.standard_normal(n), rng.standard_normal(n)
+    y = run_sym(cuda, srp, sci, sv, d, x, alpha, beta, y0.copy())
+    assert rel_l2(y, OK.symv(srp, sci, sv, d, x, alpha, beta, y0)) < TOL
+
+
+def test_float32_twins(cuda):
+    rng = np.random.default_rng(6)
+    n1 = 16
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    x = rng.standard_normal(N).astype(np.float32)
+    y, _ = run_general(cuda, rp, col, val.astype(np.float32), x, N, dtype=torch.float32)
+    assert np.array_equal(y, OK.spmv(rp, col, val.astype(np.float32), x))
+    srp, sci, sv, d = split_symmetric(rp, col, val)
+    ys = run_sym(cuda, srp, sci, sv.astype(np.float32), d.astype(np.float32), x, dtype=torch.float32)
+    assert rel_l2(ys, OK.symv(srp, sci, sv.astype(np.float32), d.astype(np.float32), x)) < 1e-5
+
+
+def test_gather_scatter(cuda):
+    rng = np.random.default_rng(7)
+    for n, m in [(0, 10), (1, 10), (1000, 5000), (131072, 2097152)]:
+        idx = rng.integers(0, m, size=n).astype(np.int32)
+        vec = rng.standard_normal(m)
+        out = torch.empty(n, dtype=torch.float64, device=cuda)
+        K.gather(torch.from_numpy(idx).to(cuda), torch.from_numpy(vec).to(cuda), out)
+        assert np.array_equal(out.cpu().numpy(), vec[idx])  # bit-exact copy (reference_executor.cpp:158-164)
+    idx = rng.integers(0, 100, size=5000).astype(np.int32)
+    src = rng.standard_normal(5000)
+    acc = rng.standard_normal(100)
+    want = acc.copy()
+    np.add.at(want, idx, src)
+    accd = torch.from_numpy(acc).to(cuda)
+    K.scatter_add(torch.from_numpy(idx).to(cuda), torch.from_numpy(src).to(cuda), accd)
+    assert rel_l2(accd.cpu().numpy(), want) < 1e-13
+
+
+def test_dot_deterministic(cuda):
+    rng = np.random.default_rng(8)
+    scratch = K.new_dot_scratch(cuda)
+    for n in [0, 1, 7, 4096, 1000003]:
+        a, b = rng.standard_normal(n), rng.standard_normal(n)
+        out = torch.zeros(2, dtype=torch.float64, device=cuda)
+        ad, bd = torch.from_numpy(a).to(cuda), torch.from_numpy(b).to(cuda)
+        K.dot(ad, bd, out[0:1], scratch)
+        K.dot(ad, bd, out[1:2], scratch)
+        got = out.cpu().numpy()
+        assert got[0] == got[1]  # run-to-run identical
+        want = OK.ddot(a, b)
+        assert abs(got[0] - want) <= 1e-13 * max(1.0, np.abs(a * b).sum())
+
+
+def _oracle_cg(rp, ci, v, b, kmax, rtol):
+    """cg.cpp:21-98 on one rank, BLAS-1 through the oracle restatement."""
+    M = len(b)
+    r, p, x = b.copy(), b.copy(), np.zeros(M)
+    rnorm0 = np.sqrt(OK.ddot(r, r))
+    rnorm_old = rnorm0
+    hist = []
+    k = 0
+    while k < kmax:
+        k += 1
+        Ap = OK.spmv(rp, ci, v, p)
+        alpha = (rnorm_old * rnorm_old) / OK.ddot(p, Ap)
+        OK.daxpy(alpha, p, x)
+        OK.daxpy(-alpha, Ap, r)
+        rnorm_new = np.sqrt(OK.ddot(r, r))
+        beta = (rnorm_new * rnorm_new) / (rnorm_old * rnorm_old)
+        rnorm_old = rnorm_new
+        hist.append(rnorm_new)
+        if rnorm_new / rnorm0 < rtol:
+            break
+        OK.dscal(beta, p)
+        OK.daxpy(1.0, r, p)
+    return k, x, np.array(hist)
+
+
+@pytest.mark.parametrize("fused_dot", [False, True])
+def test_cg_kernels_single_rank(cuda, fused_dot):
+    n1 = 16
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    b = OK.spmv(rp, col, val, np.ones(N))
+    kmax, rtol = 200, 1e-8
+    k_ref, x_ref, hist_ref = _oracle_cg(rp, col, val, b, kmax, rtol)
+
+    rpd, cid, vd = dev_csr(rp, col, val, cuda)
+    plan = K.CsrPlan(N, N, rpd, False)
+    bd = torch.from_numpy(b).to(cuda)
+    r, p, x, Ap = bd.clone(), bd.clone(), torch.zeros_like(bd), torch.empty_like(bd)
+    st = K.new_cg_state(cuda)
+    scratch = K.new_dot_scratch(cuda)
+    hist = torch.zeros(kmax, dtype=torch.float64, device=cuda)
+    rr = torch.zeros(1, dtype=torch.float64, device=cuda)
+    K.dot(r, r, rr, scratch)
+    K.cg_init_state(st, rr, rtol, kmax)
+    for _ in range(k_ref + 5):  # extra iterations must be no-ops once done
+        if fused_dot:
+            K.spmv_dot(plan, rpd, cid, vd, p, Ap, st[1:2])
+        else:
+            K.spmv(plan, rpd, cid, vd, p, Ap)
+            K.dot(p, Ap, st[1:2], scratch, st[4:5])
+        K.cg_update_xr(N, st, p, Ap, x, r)
+        K.cg_update_p(N, st, r, p, hist)
+    torch.cuda.synchronize()
+    s = st.cpu().numpy()
+    k = int(s[5])
+    assert s[4] == 1.0
+    assert abs(k - k_ref) <= 1  # BASELINE.json: iteration counts within +-1
+    m = min(k, k_ref)
+    h = hist.cpu().numpy()[:m]
+    # BASELINE.json: residual histories within 1e-10 relative (to the initial residual)
+    assert np.max(np.abs(h - hist_ref[:m])) / hist_ref[0] < 1e-10
+    assert rel_l2(x.cpu().numpy(), x_ref) < 1e-9
+    plan.close()
+
+
+@pytest.mark.parametrize("stencil", [7, 27])
+@pytest.mark.parametrize("slab", [(0, 6, 6), (0, 3, 6), (2, 4, 6), (5, 6, 6)])
+def test_device_generator_matches_host(cuda, stencil, slab):
+    z0, z1, nzg = slab
+    nx, ny = 5, 4
+    rp, col, val = synth.laplace3d_rows(nx, ny, nzg, z0, z1, stencil)
+    c0, c1 = nx * ny * z0, nx * ny * z1
+    local, ghosts = synth.localize_columns(col, c0, c1)
+    n = c1 - c0
+    # rows sorted by local column id, as setFromTriplets leaves them (Matrix.cpp:427-428)
+    rows = np.repeat(np.arange(n), np.diff(rp))
+    order = np.lexsort((local, rows))
+    local, valo = local[order], val[order]
+    g = K.laplace3d(nx, ny, nzg, z0, z1, stencil, 0, cuda)
+    assert g["nghosts"] == len(ghosts)
+    assert np.array_equal(g["local"][0].cpu().numpy(), rp.astype(np.int32))
+    assert np.array_equal(g["local"][1].cpu().numpy(), local)
+    assert np.array_equal(g["local"][2].cpu().numpy(), valo)
+    # symmetric split (Matrix.cpp:337-349): strictly lower owned / diagonal / ghosts
+    s = K.laplace3d(nx, ny, nzg, z0, z1, stencil, 1, cuda)
+    owned = local < n
+    lower = owned & (local < rows)
+    assert np.array_equal(s["local"][1].cpu().numpy(), local[lower])
+    assert np.array_equal(s["remote"][1].cpu().numpy(), local[~owned])
+    assert np.array_equal(s["diag"].cpu().numpy(), np.full(n, 6.0 if stencil == 7 else 26.0))
+    assert np.array_equal(s["local"][0].cpu().numpy(), np.concatenate([[0], np.cumsum(np.bincount(rows[lower], minlength=n))]))
+    # overlap split (Matrix.cpp:350-355)
+    o = K.laplace3d(nx, ny, nzg, z0, z1, stencil, 2, cuda)
+    assert np.array_equal(o["local"][1].cpu().numpy(), local[owned])
+    assert np.array_equal(o["remote"][1].cpu().numpy(), local[~owned])
+    assert np.array_equal(o["remote"][2].cpu().numpy(), valo[~owned])
+
+
+def test_full_size_properties(cuda):
+    """BASELINE.json size (27-point 256^3): exact checksum of A*1 and linearity."""
+    n1 = 256
+    N = n1 ** 3
+    g = K.laplace3d(n1, n1, n1, 0, n1, 27, 0, cuda)
+    rp, ci, v = g["local"]
+    nnz = int(rp[-1].item())
+    assert nnz == (3 * n1 - 2) ** 3  # 449 455 096
+    plan = K.CsrPlan(N, N, rp, False)
+    ones = torch.ones(N, dtype=torch.float64, device=cuda)
+    y = torch.empty_like(ones)
+    K.spmv(plan, rp, ci, v, ones, y)
+    # row sum = 26 - (#neighbours): integers, exact; total = 27 N - nnz
+    assert float(y.sum().item()) == float(27 * N - nnz)
+    assert float(y.min().item()) == 0.0 and float(y.max().item()) == 19.0  # corner row: 26 - 7
+    # linearity: A(2a + b) == 2 A a + A b up to rounding
+    a = torch.from_numpy(synth.bump_vector(N, 0, N)).to(cuda)
+    ya, yab = torch.empty_like(a), torch.empty_like(a)
+    K.spmv(plan, rp, ci, v, a, ya)
+    K.spmv(plan, rp, ci, v, 2 * a + ones, yab)
+    assert float(((2 * ya + y) - yab).norm() / yab.norm()) < 1e-13
+    # fused dot epilogue equals x.y
+    d = torch.zeros(1, dtype=torch.float64, device=cuda)
+    K.spmv_dot(plan, rp, ci, v, a, ya, d)
+    assert abs(float(d.item()) - float(torch.dot(a, ya).item())) <= 1e-12 * abs(float(d.item()))
+    plan.close()
+    # symmetric storage, 7-point 256^3 (config 2): same operator as general storage
+    s = K.laplace3d(n1, n1, n1, 0, n1, 7, 1, cuda)
+    g7 = K.laplace3d(n1, n1, n1, 0, n1, 7, 0, cuda)
+    ps = K.CsrPlan(N, N, s["local"][0], True)
+    pg = K.CsrPlan(N, N, g7["local"][0], False)
+    ys, yg = torch.empty_like(a), torch.empty_like(a)
+    K.symv(ps, *s["local"], s["diag"], a, ys)
+    K.spmv(pg, *g7["local"], a, yg)
+    assert float((ys - yg).norm() / yg.norm()) < TOL
+    ps.close()
+    pg.close()
