@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200spmv.so")
+LIB_PATH = os.environ.get("B200SPMV_LIB") or os.path.join(_HERE, "lib", "libb200spmv.so")
 
 
 class B200Error(RuntimeError):

@@ -33,6 +33,10 @@
 namespace b200
 {
 
+#ifndef B200_WALK_CHUNK
+#define B200_WALK_CHUNK 16
+#endif
+constexpr int WALK_CHUNK = B200_WALK_CHUNK;
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
 constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
 constexpr int MAX_STAGE_BYTES = 96 * 1024;
@@ -166,31 +170,29 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
       xi = __ldg(a.x + r);
       sum = mul_rn(__ldg(a.diag + r), xi);
     }
-    int j = rs;
-    for (; j + 4 <= re; j += 4) {
-      const int c0 = sc[j - L.lo_c], c1 = sc[j + 1 - L.lo_c];
-      const int c2 = sc[j + 2 - L.lo_c], c3 = sc[j + 3 - L.lo_c];
-      const T v0 = sv[j - L.lo_v], v1 = sv[j + 1 - L.lo_v];
-      const T v2 = sv[j + 2 - L.lo_v], v3 = sv[j + 3 - L.lo_v];
-      const T x0 = __ldg(a.x + c0), x1 = __ldg(a.x + c1);
-      const T x2 = __ldg(a.x + c2), x3 = __ldg(a.x + c3);
-      sum = add_rn(sum, mul_rn(v0, x0));
-      sum = add_rn(sum, mul_rn(v1, x1));
-      sum = add_rn(sum, mul_rn(v2, x2));
-      sum = add_rn(sum, mul_rn(v3, x3));
-      if (SYM) {
-        red_add(a.y + c0, mul_rn(mul_rn(a.alpha, v0), xi));
-        red_add(a.y + c1, mul_rn(mul_rn(a.alpha, v1), xi));
-        red_add(a.y + c2, mul_rn(mul_rn(a.alpha, v2), xi));
-        red_add(a.y + c3, mul_rn(mul_rn(a.alpha, v3), xi));
+    // Chunks of WALK_CHUNK entries: all column indices, values and x gathers of a
+    // chunk are issued before the first add, so one row keeps up to WALK_CHUNK
+    // independent L2-latency gathers in flight; the adds then run in j order.
+    for (int base = rs; base < re; base += WALK_CHUNK) {
+      int c[WALK_CHUNK];
+      T v[WALK_CHUNK], xv[WALK_CHUNK];
+#pragma unroll
+      for (int u = 0; u < WALK_CHUNK; ++u) {
+        const bool ok = base + u < re;
+        c[u] = ok ? sc[base + u - L.lo_c] : 0;
+        v[u] = ok ? sv[base + u - L.lo_v] : T(0);
       }
-    }
-    for (; j < re; ++j) {
-      const int c = sc[j - L.lo_c];
-      const T v = sv[j - L.lo_v];
-      sum = add_rn(sum, mul_rn(v, __ldg(a.x + c)));
-      if (SYM)
-        red_add(a.y + c, mul_rn(mul_rn(a.alpha, v), xi));
+#pragma unroll
+      for (int u = 0; u < WALK_CHUNK; ++u)
+        xv[u] = (base + u < re) ? __ldg(a.x + c[u]) : T(0);
+#pragma unroll
+      for (int u = 0; u < WALK_CHUNK; ++u) {
+        if (base + u < re) {
+          sum = add_rn(sum, mul_rn(v[u], xv[u]));
+          if (SYM)
+            red_add(a.y + c[u], mul_rn(mul_rn(a.alpha, v[u]), xi));
+        }
+      }
     }
     const T out = store_row<T, SYM>(a, r, sum);
     if (DOT)
@@ -698,8 +700,8 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   p->nnz = nnz;
   p->symmetric = symmetric ? 1 : 0;
   int rc = plan_apply_tuning(p, env_int("B200_SPMV_VARIANT", 0),
-                             env_int("B200_SPMV_TILE_BYTES", 32 * 1024),
-                             env_int("B200_SPMV_STAGES", 3), env_int("B200_SPMV_CWARPS", 4),
+                             env_int("B200_SPMV_TILE_BYTES", 48 * 1024),
+                             env_int("B200_SPMV_STAGES", 2), env_int("B200_SPMV_CWARPS", 8),
                              env_int("B200_SPMV_CTAS", 2));
   if (rc) {
     delete p;

@@ -36,7 +36,7 @@ class CsrPlan:
         check(lib().b200_csr_plan_info(self.h, C.byref(nt), C.byref(mx), hist))
         return {"num_tiles": nt.value, "max_row_len": mx.value, "hist": list(hist)}
 
-    def tune(self, variant=0, tile_bytes=32768, stages=3, consumer_warps=4, ctas_per_sm=2):
+    def tune(self, variant=0, tile_bytes=49152, stages=2, consumer_warps=8, ctas_per_sm=2):
         check(lib().b200_csr_plan_tune(self.h, _ptr(self.rowptr), variant, tile_bytes, stages,
                                        consumer_warps, ctas_per_sm, _stream()))
 
