@@ -1,0 +1,108 @@
+// L2GMap.h -- local-to-global map and halo plan (reference: spmv/L2GMap.h:24-196).
+//
+// A rank owns a contiguous range of global indices; indices owned elsewhere are
+// "ghosts" stored after the owned entries of every vector ([owned | ghosts ascending]).
+// The constructor computes the exchange plan exactly as the reference's default
+// branch does (L2GMap.cpp:346-479; semantics in SURVEY.md Appendix A) -- those
+// integer artefacts are bit-identical to the reference's.  update() moves ghost
+// values with a pack kernel + grouped NCCL send/recv instead of MPI.
+#pragma once
+
+#include "config.h"
+#include "spmv_export.h"
+
+#include "mpi_utils.h"
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <mpi.h>
+#include <vector>
+
+namespace spmv
+{
+
+class DeviceExecutor;
+
+class SPMV_EXPORT L2GMap
+{
+public:
+  /// @param comm        communicator (collective call)
+  /// @param local_size  number of owned entries
+  /// @param ghosts      global indices owned by other ranks, sorted ascending
+  /// @param exec        executor that holds the pack index list and send buffer
+  /// @param cm          communication model (see mpi_utils.h)
+  /// Throws std::runtime_error for unsorted ghosts, a ghost inside the local range
+  /// (L2GMap.cpp:362-363,371-372) or an out-of-scope model.
+  L2GMap(MPI_Comm comm, std::int64_t local_size, const std::vector<std::int64_t>& ghosts,
+         std::shared_ptr<spmv::DeviceExecutor> exec,
+         CommunicationModel cm = CommunicationModel::collective_blocking);
+  ~L2GMap();
+  L2GMap(const L2GMap&) = delete;
+  L2GMap& operator=(const L2GMap&) = delete;
+
+  std::int32_t local_size() const;
+  std::int32_t num_ghosts() const;
+  std::int64_t global_size() const;
+  std::int64_t global_offset() const;
+  std::int32_t global_to_local(std::int64_t i) const;
+  bool overlapping() const;
+  MPI_Comm global_comm() const { return _comm; }
+  int rank() const { return _mpi_rank; }
+  const std::vector<std::int64_t>& ghosts() const { return _ghosts; }
+
+  /// Forward halo: owners' values -> ghost tail of vec_data (executor memory with
+  /// room for local_size()+num_ghosts()).  Blocking models: complete in stream order
+  /// on the executor's stream.  Non-blocking models: started on the side stream;
+  /// update_finalise() makes the executor's stream wait for the arrival.
+  template <typename T>
+  void update(T* vec_data) const;
+  template <typename T>
+  void update_finalise(T* vec_data) const;
+  /// Reverse halo: ghost values -> added onto their owners' entries
+  /// (L2GMap.cpp:908-959), exchange + scatter-add kernel.
+  template <typename T>
+  void reverse_update(T* vec_data) const;
+
+  // ---- the plan, for inspection (private in the reference; exposed read-only so
+  //      parity of the integer artefacts can be tested) ----
+  const std::vector<std::int64_t>& ranges() const { return _ranges; }
+  const std::vector<int>& neighbours() const { return _neighbours; }
+  /// what this rank RECEIVES in update() per neighbour (its ghosts), and where:
+  /// offsets already shifted by local_size (L2GMap.cpp:460-461)
+  const std::vector<std::int32_t>& send_count() const { return _send_count; }
+  const std::vector<std::int32_t>& send_offset() const { return _send_offset; }
+  /// what this rank SENDS in update() per neighbour (slices of the packed buffer)
+  const std::vector<std::int32_t>& recv_count() const { return _recv_count; }
+  const std::vector<std::int32_t>& recv_offset() const { return _recv_offset; }
+  /// owner-local indices to pack, neighbour by neighbour (host copy of _indexbuf)
+  const std::vector<std::int32_t>& indexbuf() const { return _indexbuf_host; }
+  CommunicationModel communication_model() const { return _cm; }
+
+private:
+  template <typename T>
+  void exchange_forward(T* vec_data, bool overlap) const;
+  template <typename T>
+  void ensure_send_buf() const;
+
+  std::shared_ptr<spmv::DeviceExecutor> _exec;
+  std::vector<std::int64_t> _ranges;
+  std::int32_t _mpi_rank = -1;
+  std::map<std::int64_t, std::int32_t> _global_to_local;
+  std::vector<std::int64_t> _ghosts;
+
+  int _num_indices = 0;
+  std::int32_t* _indexbuf = nullptr; // executor memory
+  std::vector<std::int32_t> _indexbuf_host;
+  std::vector<std::int32_t> _send_count, _recv_count, _send_offset, _recv_offset;
+  std::vector<int> _neighbours;
+
+  MPI_Comm _comm = MPI_COMM_NULL;
+  CommunicationModel _cm = CommunicationModel::collective_blocking;
+  mutable void* _send_buf = nullptr; // executor memory, lazily allocated (L2GMap.cpp:507-514)
+  mutable size_t _send_buf_bytes = 0;
+  mutable void* _recv_buf = nullptr; // reverse_update staging
+  mutable size_t _recv_buf_bytes = 0;
+};
+
+} // namespace spmv

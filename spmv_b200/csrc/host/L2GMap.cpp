@@ -1,0 +1,245 @@
+// L2GMap.cpp -- halo plan construction and the NCCL-based ghost exchange.
+// Reference: spmv/L2GMap.cpp:346-479 (plan, default branch), :502-642 (update
+// variants), :868-959 (dispatch, reverse update).  The plan's integer artefacts are
+// defined by SURVEY.md Appendix A and must equal the reference's bit for bit.
+#include "L2GMap.h"
+
+#include "b200_executor.h"
+#include "device_executor.h"
+#include "host_util.h"
+
+#include <algorithm>
+#include <stdexcept>
+
+using namespace spmv;
+
+namespace
+{
+const B200Executor* as_b200(const std::shared_ptr<DeviceExecutor>& e)
+{
+  return dynamic_cast<const B200Executor*>(e.get());
+}
+} // namespace
+
+//-----------------------------------------------------------------------------
+L2GMap::L2GMap(MPI_Comm comm, std::int64_t local_size, const std::vector<std::int64_t>& ghosts,
+               std::shared_ptr<DeviceExecutor> exec, CommunicationModel cm)
+    : _exec(exec), _ghosts(ghosts), _comm(comm), _cm(cm)
+{
+  if (cm != CommunicationModel::p2p_blocking && cm != CommunicationModel::p2p_nonblocking
+      && cm != CommunicationModel::collective_blocking && cm != CommunicationModel::collective_nonblocking)
+    throw std::runtime_error("L2GMap: one-sided / shared-memory communication models are MPI-RMA specific "
+                             "and not provided by the B200 build");
+
+  int mpi_size = 0;
+  CHECK_MPI(MPI_Comm_size(comm, &mpi_size));
+  CHECK_MPI(MPI_Comm_rank(comm, &_mpi_rank));
+
+  // Step 1: ownership ranges = exclusive prefix sum of everybody's local size
+  _ranges.assign(mpi_size + 1, 0);
+  CHECK_MPI(MPI_Allgather(&local_size, 1, MPI_INT64_T, _ranges.data() + 1, 1, MPI_INT64_T, comm));
+  for (int i = 0; i < mpi_size; ++i)
+    _ranges[i + 1] += _ranges[i];
+  const std::int64_t r0 = _ranges[_mpi_rank], r1 = _ranges[_mpi_rank + 1];
+
+  if (!std::is_sorted(_ghosts.begin(), _ghosts.end()))
+    throw std::runtime_error("Ghosts must be sorted");
+
+  // Step 2: owner, owner-local index and local slot of every ghost
+  std::vector<std::int32_t> ghost_count(mpi_size, 0);
+  std::vector<std::int32_t> ghost_local(_ghosts.size());
+  for (std::size_t k = 0; k < _ghosts.size(); ++k) {
+    const std::int64_t g = _ghosts[k];
+    if (g >= r0 && g < r1)
+      throw std::runtime_error("Ghost index in local range");
+    if (g < 0 || g >= _ranges.back())
+      throw std::runtime_error("Ghost index outside the global range");
+    _global_to_local.insert({g, static_cast<std::int32_t>(local_size + k)});
+    const int p = static_cast<int>(std::upper_bound(_ranges.begin(), _ranges.end(), g) - _ranges.begin()) - 1;
+    ++ghost_count[p];
+    ghost_local[k] = static_cast<std::int32_t>(g - _ranges[p]);
+  }
+
+  // Step 3: who wants how many of my entries
+  std::vector<std::int32_t> remote_count(mpi_size, 0);
+  CHECK_MPI(MPI_Alltoall(ghost_count.data(), 1, MPI_INT, remote_count.data(), 1, MPI_INT, comm));
+
+  // Step 4: symmetric neighbour list, ascending rank; zero counts kept so the
+  // count arrays line up with _neighbours
+  for (int q = 0; q < mpi_size; ++q) {
+    if (ghost_count[q] > 0 || remote_count[q] > 0) {
+      _neighbours.push_back(q);
+      _send_count.push_back(ghost_count[q]);
+      _recv_count.push_back(remote_count[q]);
+    }
+  }
+  const int nnbr = static_cast<int>(_neighbours.size());
+  if (nnbr == 0) {
+    _send_count = {0};
+    _recv_count = {0};
+  }
+
+  // Step 5: exclusive scans with the total appended
+  _send_offset = {0};
+  for (std::int32_t c : _send_count)
+    _send_offset.push_back(_send_offset.back() + c);
+  _recv_offset = {0};
+  for (std::int32_t c : _recv_count)
+    _recv_offset.push_back(_recv_offset.back() + c);
+  _num_indices = _recv_offset.back();
+
+  // Step 6: tell every owner which of its entries I need (owner-local indices, in my
+  // ghost order); what arrives is my pack list, neighbour by neighbour
+  _indexbuf_host.assign(_num_indices, 0);
+  {
+    MPI_Comm nbr_comm = MPI_COMM_NULL;
+    CHECK_MPI(MPI_Dist_graph_create_adjacent(comm, nnbr, _neighbours.data(), MPI_UNWEIGHTED, nnbr,
+                                             _neighbours.data(), MPI_UNWEIGHTED, MPI_INFO_NULL, false,
+                                             &nbr_comm));
+    CHECK_MPI(MPI_Neighbor_alltoallv(ghost_local.data(), _send_count.data(), _send_offset.data(),
+                                     MPI_INT32_T, _indexbuf_host.data(), _recv_count.data(),
+                                     _recv_offset.data(), MPI_INT32_T, nbr_comm));
+    CHECK_MPI(MPI_Comm_free(&nbr_comm));
+  }
+
+  // Step 8: offsets now address the ghost tail of a vector directly
+  for (std::int32_t& s : _send_offset)
+    s += static_cast<std::int32_t>(local_size);
+
+  if (_num_indices > 0) {
+    _indexbuf = _exec->alloc<std::int32_t>(_num_indices);
+    _exec->copy_from<std::int32_t>(_indexbuf, _exec->get_host(), _indexbuf_host.data(), _num_indices);
+  }
+
+  // The NCCL communicator is created once per executor, collectively.
+  if (const B200Executor* gpu = as_b200(_exec))
+    gpu->attach_comm(comm);
+}
+//-----------------------------------------------------------------------------
+L2GMap::~L2GMap()
+{
+  // (the reference leaks _indexbuf and, for blocking models, _send_buf:
+  //  L2GMap.cpp:482-499)
+  try {
+    _exec->synchronize();
+  } catch (...) {
+  }
+  _exec->free(_indexbuf);
+  _exec->free(_send_buf);
+  _exec->free(_recv_buf);
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::ensure_send_buf() const
+{
+  const size_t need = sizeof(T) * static_cast<size_t>(std::max(_num_indices, 1));
+  if (_send_buf == nullptr || _send_buf_bytes < need) {
+    _exec->free(_send_buf);
+    _send_buf = _exec->alloc<char>(need);
+    _send_buf_bytes = need;
+  }
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::exchange_forward(T* vec_data, bool overlap) const
+{
+  ensure_send_buf<T>();
+  // pack: send_buf[k] = vec[indexbuf[k]]  (throws on the host executor: no CPU path)
+  _exec->gather_ghosts_run(_num_indices, _indexbuf, vec_data, static_cast<T*>(_send_buf));
+
+  const B200Executor* gpu = as_b200(_exec);
+  if (gpu == nullptr)
+    throw std::runtime_error("L2GMap::update needs the B200 executor");
+  const int nnbr = static_cast<int>(_neighbours.size());
+  if (nnbr == 0)
+    return;
+  detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  void* stream = gpu->get_cuda_stream();
+  if (overlap) {
+    // side stream: starts once the pack is done, signals arrival with an event
+    detail::check(b200_event_record(gpu->packed_event(), gpu->get_cuda_stream()), "event record");
+    detail::check(b200_stream_wait_event(gpu->comm_stream(), gpu->packed_event()), "stream wait");
+    stream = gpu->comm_stream();
+  }
+  // NB the naming (L2GMap.cpp:520-525): _recv_* describe what I SEND in a forward
+  // update, _send_* what I RECEIVE (my ghosts), landing straight in the tail of vec_data.
+  detail::check(b200_halo_exchange(gpu->nccl_comm(), nnbr, _neighbours.data(), _send_buf, _recv_count.data(),
+                                   _recv_offset.data(), vec_data, _send_count.data(), _send_offset.data(),
+                                   static_cast<int>(sizeof(T)), stream),
+                "halo exchange");
+  if (overlap)
+    detail::check(b200_event_record(gpu->arrived_event(), gpu->comm_stream()), "event record");
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::update(T* vec_data) const
+{
+  exchange_forward(vec_data, overlapping());
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::update_finalise(T*) const
+{
+  if (!overlapping() || _neighbours.empty())
+    return;
+  const B200Executor* gpu = as_b200(_exec);
+  if (gpu == nullptr)
+    throw std::runtime_error("L2GMap::update_finalise needs the B200 executor");
+  detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  detail::check(b200_stream_wait_event(gpu->get_cuda_stream(), gpu->arrived_event()), "stream wait");
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::reverse_update(T* vec_data) const
+{
+  // The reference acts only for the two blocking models and is host-only
+  // (L2GMap.cpp:908-959); here every in-scope model sends the ghost tail to the
+  // owners and accumulates with a scatter-add kernel, in stream order.
+  const B200Executor* gpu = as_b200(_exec);
+  if (gpu == nullptr)
+    throw std::runtime_error("L2GMap::reverse_update needs the B200 executor");
+  const int nnbr = static_cast<int>(_neighbours.size());
+  if (nnbr == 0)
+    return;
+  const size_t need = sizeof(T) * static_cast<size_t>(std::max(_num_indices, 1));
+  if (_recv_buf == nullptr || _recv_buf_bytes < need) {
+    _exec->free(_recv_buf);
+    _recv_buf = _exec->alloc<char>(need);
+    _recv_buf_bytes = need;
+  }
+  detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  detail::check(b200_halo_exchange(gpu->nccl_comm(), nnbr, _neighbours.data(), vec_data, _send_count.data(),
+                                   _send_offset.data(), _recv_buf, _recv_count.data(), _recv_offset.data(),
+                                   static_cast<int>(sizeof(T)), gpu->get_cuda_stream()),
+                "reverse halo exchange");
+  gpu->scatter_add_run(_num_indices, _indexbuf, static_cast<const T*>(_recv_buf), vec_data);
+}
+//-----------------------------------------------------------------------------
+std::int32_t L2GMap::global_to_local(std::int64_t i) const
+{
+  const std::int64_t r0 = _ranges[_mpi_rank], r1 = _ranges[_mpi_rank + 1];
+  if (i >= r0 && i < r1)
+    return static_cast<std::int32_t>(i - r0);
+  auto it = _global_to_local.find(i);
+  if (it == _global_to_local.end())
+    throw std::runtime_error("L2GMap::global_to_local: index is neither owned nor a ghost");
+  return it->second;
+}
+bool L2GMap::overlapping() const
+{
+  return _cm == CommunicationModel::p2p_nonblocking || _cm == CommunicationModel::collective_nonblocking;
+}
+std::int32_t L2GMap::local_size() const
+{
+  return static_cast<std::int32_t>(_ranges[_mpi_rank + 1] - _ranges[_mpi_rank]);
+}
+std::int32_t L2GMap::num_ghosts() const { return static_cast<std::int32_t>(_ghosts.size()); }
+std::int64_t L2GMap::global_size() const { return _ranges.back(); }
+std::int64_t L2GMap::global_offset() const { return _ranges[_mpi_rank]; }
+//-----------------------------------------------------------------------------
+template void spmv::L2GMap::update<double>(double*) const;
+template void spmv::L2GMap::update<float>(float*) const;
+template void spmv::L2GMap::update_finalise<double>(double*) const;
+template void spmv::L2GMap::update_finalise<float>(float*) const;
+template void spmv::L2GMap::reverse_update<double>(double*) const;
+template void spmv::L2GMap::reverse_update<float>(float*) const;
