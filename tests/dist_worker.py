@@ -1,0 +1,189 @@
+"""Multi-process worker for the distributed tests (launched by torch.distributed.run).
+
+mode cpu : gloo, host executor -- the N>1 host logic (halo plan, create_matrix split,
+           read_petsc, create_A) over the torch.distributed transport, checked against
+           the reference's own code run with thread-ranks (oracle/_ref) or, where that
+           library is absent, against the committed golden fixtures.
+mode gpu : nccl, one rank per GPU -- update + mult and CG through the whole stack,
+           checked against the same oracle.
+Exit code 0 = all checks passed on this rank.
+"""
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from oracle import ref_api as R  # noqa: E402
+from spmv_b200 import api, synth  # noqa: E402
+from tests import cases  # noqa: E402
+from tests.fixtures import rel_l2  # noqa: E402
+
+TOL_Y = 1e-12
+
+
+def reference_world(size, rows, N, sym, cm, want_cg=None, x_fn=None):
+    """Run the reference on `size` thread-ranks; returns per-rank dicts."""
+    out = {}
+
+    def body(rank):
+        inp = cases.local_inputs(rows, N, rank, size)
+        A = R.RefMatrix.create_matrix(inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                      inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
+        plan = A.plan(0)
+        d = {"plan": plan, "rowplan": A.plan(1), "local": A.block(0), "remote": A.block(1), "info": A.info()}
+        n_pad = plan["local_size"] + plan["num_ghosts"]
+        x = np.zeros(n_pad)
+        x[: plan["local_size"]] = x_fn(inp["r0"], inp["r1"])
+        y = np.zeros(inp["nrows_local"])
+        A.update(x)
+        A.mult(x, y)
+        d["x"], d["y"] = x, y
+        if want_cg:
+            ones = np.zeros(n_pad)
+            ones[: plan["local_size"]] = 1.0
+            b = np.zeros(inp["nrows_local"])
+            A.update(ones)
+            A.mult(ones, b)
+            d["b"] = b
+            d["cg_it"], d["cg_x"] = A.cg(b, *want_cg)
+        out[rank] = d
+        A.close()
+
+    R.run_ranks(size, body)
+    return out
+
+
+def main():
+    mode = sys.argv[1]
+    rank, size = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    if mode == "gpu":
+        dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+        torch.cuda.set_device(dev)
+        dist.init_process_group("nccl", device_id=dev)
+        setup_group = dist.new_group(backend="gloo")
+    else:
+        dist.init_process_group("gloo")
+        setup_group = None
+    api.init_world_from_torch(setup_group)
+    assert api.world_rank() == rank and api.world_size() == size
+    ex = api.B200Executor.create(dev.index) if mode == "gpu" else api.ReferenceExecutor.create()
+    have_ref = R.available()
+    failures = []
+
+    def check(cond, what):
+        if not cond:
+            failures.append(what)
+
+    problems = [("fixture", None), ("lap27", (6, 5, 8)), ("lap7", (7, 6, 8)), ("powerlaw", 4000), ("create_a", 1001)]
+    combos = [(False, api.P2P_BLOCKING), (False, api.P2P_NONBLOCKING), (False, api.COLLECTIVE_BLOCKING),
+              (False, api.COLLECTIVE_NONBLOCKING), (True, api.COLLECTIVE_BLOCKING), (True, api.P2P_NONBLOCKING)]
+    for kind, n in problems:
+        N, rows = cases.make_problem(kind, n)
+        x_fn = lambda r0, r1: synth.bump_vector(N, r0, r1) + 0.1  # noqa: E731
+        for sym, cm in combos:
+            if sym and kind == "powerlaw":
+                continue
+            tag = f"{kind} size={size} sym={sym} cm={cm}"
+            want_cg = (200, 1e-8) if (mode == "gpu" and kind in ("lap27", "lap7", "create_a")) else None
+            ref = reference_world(size, rows, N, sym, cm, want_cg, x_fn)[rank] if have_ref else None
+            inp = cases.local_inputs(rows, N, rank, size)
+            A = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                         inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
+            plan = A.col_map().plan()
+            if ref is not None:
+                check(cases.same_plan(plan, ref["plan"]), tag + ": column map plan differs")
+                check(cases.same_plan(A.row_map().plan(), ref["rowplan"]), tag + ": row map plan differs")
+                check(cases.same_block(A.local_block(), ref["local"]), tag + ": local block differs")
+                check(cases.same_block(A.remote_block(), ref["remote"]), tag + ": remote block differs")
+                check(A.non_zeros() == ref["info"]["non_zeros"], tag + ": non_zeros differs")
+            if mode == "cpu":
+                # there is no CPU compute path: update must refuse, not fall back
+                xh = np.zeros(plan["local_size"] + plan["num_ghosts"])
+                try:
+                    A.col_map().update(xh.ctypes.data)
+                    check(False, tag + ": update ran on the host executor")
+                except api.B200Error:
+                    pass
+            elif ref is not None:
+                n_pad = plan["local_size"] + plan["num_ghosts"]
+                x = torch.zeros(n_pad, dtype=torch.float64, device=dev)
+                x[: plan["local_size"]] = torch.from_numpy(x_fn(inp["r0"], inp["r1"])).to(dev)
+                y = torch.full((inp["nrows_local"],), float("nan"), dtype=torch.float64, device=dev)
+                A.col_map().update(x)
+                A.mult(x, y)
+                ex.synchronize()
+                check(np.array_equal(x.cpu().numpy(), ref["x"]), tag + ": ghost values differ after update")
+                check(rel_l2(y.cpu().numpy(), ref["y"]) < TOL_Y or np.array_equal(y.cpu().numpy(), ref["y"]),
+                      tag + f": y rel err {rel_l2(y.cpu().numpy(), ref['y'])}")
+                if want_cg:
+                    b = torch.from_numpy(ref["b"]).to(dev)
+                    xs = torch.zeros_like(b)
+                    it, hist = api.cg(ex, A, b, xs, want_cg[0], want_cg[1], history=True)
+                    check(abs(it - ref["cg_it"]) <= 1, tag + f": cg iterations {it} vs {ref['cg_it']}")
+                    xr = ref["cg_x"]
+                    err = np.linalg.norm(xs.cpu().numpy() - xr) / max(np.linalg.norm(xr), 1e-300)
+                    check(err < 1e-7, tag + f": cg x rel err {err}")
+            A.close()
+
+    # read_petsc + create_A builders over the multi-process transport
+    N, rows = cases.make_problem("powerlaw", 3000)
+    rp, col, val = rows(0, N)
+    path = os.path.join(tempfile.gettempdir(), f"spmv_b200_dist_{os.environ.get('MASTER_PORT', '0')}.petsc")
+    if rank == 0:
+        api.write_petsc_binary_matrix(path, N, N, rp, col, val)
+    dist.barrier()
+    for sym, cm in [(False, api.COLLECTIVE_BLOCKING), (False, api.P2P_NONBLOCKING)]:
+        A = api.read_petsc_binary_matrix(path, ex, sym, cm)
+        if have_ref:
+            got = {}
+
+            def body(r):
+                M = R.RefMatrix.read_petsc(path, sym, cm)
+                if r == rank:
+                    got["plan"], got["local"], got["remote"] = M.plan(0), M.block(0), M.block(1)
+                M.close()
+
+            R.run_ranks(size, body)
+            check(cases.same_plan(A.col_map().plan(), got["plan"]), f"read_petsc cm={cm}: plan differs")
+            check(cases.same_block(A.local_block(), got["local"]), f"read_petsc cm={cm}: local block differs")
+            check(cases.same_block(A.remote_block(), got["remote"]), f"read_petsc cm={cm}: remote block differs")
+        A.close()
+    A = api.create_A(1000, ex)
+    if have_ref:
+        got = {}
+
+        def body2(r):
+            M = R.RefMatrix.create_A(1000)
+            if r == rank:
+                got["plan"], got["local"] = M.plan(0), M.block(0)
+            M.close()
+
+        R.run_ranks(size, body2)
+        check(cases.same_plan(A.col_map().plan(), got["plan"]), "create_A: plan differs")
+        check(cases.same_block(A.local_block(), got["local"]), "create_A: block differs")
+    A.close()
+    dist.barrier()
+    if rank == 0 and os.path.exists(path):
+        os.remove(path)
+
+    for f in failures[:20]:
+        print(f"[rank {rank}] FAIL {f}", flush=True)
+    ok = torch.tensor([0 if failures else 1])
+    if mode == "gpu":
+        ok = ok.to(dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("DIST_OK" if int(ok.item()) == 1 else "DIST_FAILED", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if int(ok.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
