@@ -56,7 +56,11 @@ struct Plan {
   int32_t cols = 0;
   int64_t nnz = 0;
   int symmetric = 0;
-  int variant = 0;
+  int variant = 0;          // 0 persistent bulk-async pipeline, 1 one tile per CTA
+  int walk = 0;             // 0 one thread per row, 1 two-phase stream walk (short / irregular rows)
+  int walk_forced = -1;     // -1: chosen from the row-length histogram
+  int32_t w_entry = 12;     // shared-memory bytes per stored entry / per row in a stage:
+  int32_t w_row = 4;        //   the weights the tile partition balances
   int32_t num_tiles = 0;
   int32_t tile_bytes = 0;   // target bytes of matrix stream per tile
   int32_t stage_bytes = 0;  // shared-memory stage size (tile_bytes + slack)

@@ -20,9 +20,19 @@
 //   * rows longer than 32 entries are walked by a whole warp afterwards; a tile
 //     that does not fit a stage (one huge row) is read directly from global
 //     memory one warp per row;
+//   * short-row matrices (mean row length below ~12, and every symmetric block)
+//     use the two-phase "stream" walk instead: phase A is entry-parallel (each
+//     thread multiplies entries tid, tid+T, ... by their gathered x and leaves
+//     the products in shared memory, so every gather of a tile is independent
+//     and in flight together, whatever the row lengths); phase B is one thread
+//     per row summing its products in j order (same rounding sequence as the
+//     row walk).  The row-length histogram taken by the plan picks the walk;
 //   * symmetric storage: the transpose contribution goes out as fire-and-forget
 //     RED.ADD.F64 (coalesced across the warp because lanes hold consecutive
 //     rows); y is pre-scaled by beta (or zeroed) because every write is an add.
+//     The tile's slices of the diagonal and of x ride in the same bulk copies,
+//     and gathers that fall inside the tile's own rows are served from that
+//     shared-memory copy of x (the diagonal block's near band).
 #include "common.cuh"
 
 #include <algorithm>
@@ -43,10 +53,10 @@ constexpr int MAX_STAGE_BYTES = 96 * 1024;
 
 struct StageMeta {
   int r0;
-  int nrows;
+  int nrows;   // rows of the tile
   int lo;
-  int hi;
-  int fits;
+  int hi;      // end of the STAGED entries (rowptr[r0 + nstaged])
+  int nstaged; // leading rows whose stream sits in the stage; the rest are read from global memory
   int nlong;
   int pad[2];
   int long_rows[LONG_CAP];
@@ -73,33 +83,45 @@ struct SpmvArgs {
 
 __host__ __device__ __forceinline__ int round16(int b) { return (b + 15) & ~15; }
 
-// Byte layout of one staged tile: [values | colind | rowptr], each slice starting
-// at the 16-byte aligned global element at or below the tile's first element.
-template <typename T>
+// Byte layout of one staged tile: [values | colind | rowptr] and, for the extended
+// (symmetric stream) layout, [diag | x | products]; each loaded slice starts at the
+// 16-byte aligned global element at or below the tile's first element.
+template <typename T, bool EXT>
 struct TileLayout {
-  int lo_v, lo_c, lo_r;
-  int bytes_v, bytes_c, bytes_r;
+  int lo_v, lo_c, lo_r, lo_d;
+  int bytes_v, bytes_c, bytes_r, bytes_d, bytes_p;
   __host__ __device__ TileLayout(int r0, int nrows, int lo, int hi)
   {
     constexpr int VA = 16 / (int)sizeof(T);
     lo_v = lo & ~(VA - 1);
     lo_c = lo & ~3;
     lo_r = r0 & ~3;
+    lo_d = r0 & ~(VA - 1);
     bytes_v = round16((hi - lo_v) * (int)sizeof(T));
     bytes_c = round16((hi - lo_c) * 4);
     bytes_r = round16((r0 + nrows + 1 - lo_r) * 4);
+    bytes_d = EXT ? round16((r0 + nrows - lo_d) * (int)sizeof(T)) : 0;
+    bytes_p = EXT ? round16((hi - lo) * (int)sizeof(T)) : 0;
   }
-  __host__ __device__ int total() const { return bytes_v + bytes_c + bytes_r; }
+  __host__ __device__ int off_c() const { return bytes_v; }
+  __host__ __device__ int off_r() const { return bytes_v + bytes_c; }
+  __host__ __device__ int off_d() const { return bytes_v + bytes_c + bytes_r; }
+  __host__ __device__ int off_x() const { return off_d() + bytes_d; }
+  __host__ __device__ int off_p() const { return off_x() + bytes_d; }
+  __host__ __device__ int loaded() const { return off_p(); }
+  __host__ __device__ int total() const { return off_p() + bytes_p; }
 };
 
 // 64-bit pre-check first: a tile holding one enormous row must not overflow the
 // int byte counts of TileLayout.
-template <typename T>
+template <typename T, bool EXT>
 __host__ __device__ __forceinline__ bool tile_fits(int r0, int nrows, int lo, int hi, int sb)
 {
-  if ((long long)(hi - lo) * (long long)(sizeof(T) + 4) + 4ll * nrows > (long long)sb)
+  const long long per_entry = (long long)sizeof(T) + 4 + (EXT ? (long long)sizeof(T) : 0);
+  const long long per_row = 4 + (EXT ? 2ll * (long long)sizeof(T) : 0);
+  if ((long long)(hi - lo) * per_entry + per_row * nrows > (long long)sb)
     return false;
-  return TileLayout<T>(r0, nrows, lo, hi).total() <= sb;
+  return TileLayout<T, EXT>(r0, nrows, lo, hi).total() <= sb;
 }
 
 // ---------------------------------------------------------------------------
@@ -149,11 +171,11 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
 {
-  const int r0 = m->r0, nrows = m->nrows, lo = m->lo, hi = m->hi;
-  const TileLayout<T> L(r0, nrows, lo, hi);
+  const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
+  const TileLayout<T, false> L(r0, nrows, lo, hi);
   const T* sv = reinterpret_cast<const T*>(stage);
-  const int* sc = reinterpret_cast<const int*>(stage + L.bytes_v);
-  const int* sr = reinterpret_cast<const int*>(stage + L.bytes_v + L.bytes_c);
+  const int* sc = reinterpret_cast<const int*>(stage + L.off_c());
+  const int* sr = reinterpret_cast<const int*>(stage + L.off_r());
   double dot = 0.0;
 
   for (int k = tid; k < nrows; k += nthreads) {
@@ -210,6 +232,111 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
           [&](int j) { return sv[j - L.lo_v]; });
       if (lane == 0) {
         const T out = store_row<T, SYM>(a, r, sum);
+        if (DOT)
+          dot += (double)__ldg(a.x + r) * (double)out;
+      }
+    }
+  }
+  return dot;
+}
+
+// Two-phase "stream" walk of a staged tile (short or irregular rows).
+//   phase A, entry-parallel: products[j] = val[j] * x[col[j]] for every staged
+//     entry, thread t taking entries t, t+T, ...: all gathers of the tile are
+//     independent, so the memory pipeline stays full whatever the row lengths.
+//     General storage overwrites val[j] in place; the symmetric (EXT) layout
+//     keeps val for the transpose scatter and uses its own products region.
+//   phase B, row-parallel: one thread per row adds its products in j order --
+//     the same sequence of roundings as csr_kernels.cpp:45-47 -- and, symmetric
+//     storage, scatters alpha*val*x[row] into y[col] (csr_kernels.cpp:33-37).
+template <typename T, bool SYM, bool LONG, bool DOT>
+__device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned char* stage,
+                                              StageMeta* m, int tid, int nthreads, int warp,
+                                              int nwarps, int lane, int bar_id)
+{
+  constexpr bool EXT = SYM;
+  constexpr int U = 4;
+  const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
+  const TileLayout<T, EXT> L(r0, nrows, lo, hi);
+  T* sv = reinterpret_cast<T*>(stage) + (lo - L.lo_v);                  // sv[j - lo]
+  const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c);
+  const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r); // sr[k]
+  const T* sd = reinterpret_cast<const T*>(stage + L.off_d()) + (r0 - L.lo_d);     // diag[r0 + k]
+  const T* sx = reinterpret_cast<const T*>(stage + L.off_x()) + (r0 - L.lo_d);     // x[r0 + k]
+  T* sp = EXT ? reinterpret_cast<T*>(stage + L.off_p()) : sv;
+  const int n = hi - lo;
+  double dot = 0.0;
+
+  for (int j0 = tid; j0 < n; j0 += nthreads * U) {
+    int c[U];
+    T v[U], xv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int j = j0 + u * nthreads;
+      const bool ok = j < n;
+      c[u] = ok ? sc[j] : r0;
+      v[u] = ok ? sv[j] : T(0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (EXT && (unsigned)(c[u] - r0) < (unsigned)nrows)
+        xv[u] = sx[c[u] - r0];
+      else
+        xv[u] = __ldg(a.x + c[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int j = j0 + u * nthreads;
+      if (j < n)
+        sp[j] = mul_rn(v[u], xv[u]);
+    }
+  }
+  named_bar_sync(bar_id, nthreads);
+
+  for (int k = tid; k < nrows; k += nthreads) {
+    const int r = r0 + k;
+    const int rs = sr[k] - lo, re = sr[k + 1] - lo;
+    if (LONG && re - rs > SHORT_ROW) {
+      const int q = atomicAdd(&m->nlong, 1);
+      m->long_rows[q] = k;
+      continue;
+    }
+    T xi = 0, sum = 0;
+    if (SYM) {
+      xi = sx[k];
+      sum = mul_rn(sd[k], xi);
+    }
+    for (int j = rs; j < re; ++j) {
+      sum = add_rn(sum, sp[j]);
+      if (SYM)
+        red_add(a.y + sc[j], mul_rn(mul_rn(a.alpha, sv[j]), xi));
+    }
+    const T out = store_row<T, SYM>(a, r, sum);
+    if (DOT)
+      dot += (double)__ldg(a.x + r) * (double)out;
+  }
+
+  if (LONG) {
+    named_bar_sync(bar_id, nthreads);
+    const int nlong = m->nlong;
+    for (int q = warp; q < nlong; q += nwarps) {
+      const int k = m->long_rows[q];
+      const int r = r0 + k;
+      const int rs = sr[k] - lo, re = sr[k + 1] - lo;
+      T xi = 0;
+      if (SYM)
+        xi = sx[k];
+      T part = 0;
+      for (int j = rs + lane; j < re; j += 32) {
+        part += sp[j];
+        if (SYM)
+          red_add(a.y + sc[j], a.alpha * sv[j] * xi);
+      }
+      part = warp_sum(part);
+      if (lane == 0) {
+        if (SYM)
+          part += sd[k] * xi;
+        const T out = store_row<T, SYM>(a, r, part);
         if (DOT)
           dot += (double)__ldg(a.x + r) * (double)out;
       }
@@ -280,10 +407,17 @@ __device__ __forceinline__ void grid_dot_reduce(double v, int tid, int nthreads,
 // ---------------------------------------------------------------------------
 // Variant 0: persistent CTAs, bulk-async staged ring, warp-specialised.
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
+//   WALK 0: one thread per row (chunked gathers);  WALK 1: two-phase stream walk.
 // ---------------------------------------------------------------------------
-template <typename T, bool SYM, bool DOT, bool LONG, int CW>
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
+  constexpr bool EXT = SYM && WALK == 1;
   extern __shared__ __align__(128) unsigned char smem[];
   const int stages = a.stages;
   const int sb = a.stage_bytes;
@@ -316,24 +450,34 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
         const int tile = blockIdx.x + it * gridDim.x;
         const int2 t0 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile);
         const int2 t1 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile + 1);
-        const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x, hi = t1.y;
-        const int fits = tile_fits<T>(r0, nrows, lo, hi, sb);
+        const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x;
+        // Stage the longest prefix of rows that fits: a tile overshoots its byte
+        // budget by at most its last row, so this drops one (long) row at most.
+        int ns = nrows, hi = t1.y;
+        while (ns > 0 && !tile_fits<T, EXT>(r0, ns, lo, hi, sb)) {
+          --ns;
+          hi = __ldg(a.rowptr + r0 + ns);
+        }
         StageMeta* m = meta + s;
         m->r0 = r0;
         m->nrows = nrows;
         m->lo = lo;
         m->hi = hi;
-        m->fits = fits;
+        m->nstaged = ns;
         m->nlong = 0;
-        if (fits) {
-          const TileLayout<T> L(r0, nrows, lo, hi);
+        if (ns > 0) {
+          const TileLayout<T, EXT> L(r0, ns, lo, hi);
           unsigned char* dst = smem + (size_t)s * sb;
-          mbar_arrive_expect_tx(full + s, (uint32_t)L.total());
+          mbar_arrive_expect_tx(full + s, (uint32_t)L.loaded());
           if (L.bytes_v > 0)
             bulk_g2s(dst, a.val + L.lo_v, L.bytes_v, full + s);
           if (L.bytes_c > 0)
-            bulk_g2s(dst + L.bytes_v, a.colind + L.lo_c, L.bytes_c, full + s);
-          bulk_g2s(dst + L.bytes_v + L.bytes_c, a.rowptr + L.lo_r, L.bytes_r, full + s);
+            bulk_g2s(dst + L.off_c(), a.colind + L.lo_c, L.bytes_c, full + s);
+          bulk_g2s(dst + L.off_r(), a.rowptr + L.lo_r, L.bytes_r, full + s);
+          if (EXT) {
+            bulk_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
+            bulk_g2s(dst + L.off_x(), a.x + L.lo_d, L.bytes_d, full + s);
+          }
         } else {
           mbar_arrive(full + s);
         }
@@ -347,11 +491,19 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
     const int s = it % stages, use = it / stages;
     mbar_wait(full + s, use & 1);
     StageMeta* m = meta + s;
-    if (m->fits)
-      dot += walk_staged<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp, CW,
-                                       lane, 1);
-    else
-      dot += walk_direct<T, SYM, DOT>(a, m->r0, m->nrows, warp, CW, lane);
+    const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
+    if (ns > 0) {
+      if (WALK == 1) {
+        dot += walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp,
+                                              CW, lane, 1);
+        fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
+      } else {
+        dot += walk_staged<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp,
+                                              CW, lane, 1);
+      }
+    }
+    if (ns < nrows)
+      dot += walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane);
     __syncwarp();
     if (lane == 0)
       mbar_arrive(empty + s);
@@ -361,8 +513,9 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
 }
 
 // ---------------------------------------------------------------------------
-// Variant 1: one tile per CTA, staged with plain vector loads.  Used when a
-// base pointer is not 16-byte aligned, and as the comparison point for variant 0.
+// Variant 1: one tile per CTA, staged with plain vector loads, row walk.  Used
+// when a base pointer is not 16-byte aligned, and as the comparison point for
+// variant 0.
 // ---------------------------------------------------------------------------
 template <typename T, bool SYM, bool LONG, int NT>
 __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
@@ -372,35 +525,40 @@ __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
   StageMeta* m = reinterpret_cast<StageMeta*>(smem + sb);
   const int tile = blockIdx.x;
   const int r0 = __ldg(a.tile_meta + 2 * tile), lo = __ldg(a.tile_meta + 2 * tile + 1);
-  const int r1 = __ldg(a.tile_meta + 2 * tile + 2), hi = __ldg(a.tile_meta + 2 * tile + 3);
+  const int r1 = __ldg(a.tile_meta + 2 * tile + 2);
   const int nrows = r1 - r0;
   if (nrows == 0)
     return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (!tile_fits<T>(r0, nrows, lo, hi, sb)) {
-    walk_direct<T, SYM, false>(a, r0, nrows, warp, NT / 32, lane);
-    return;
+  int ns = nrows, hi = __ldg(a.tile_meta + 2 * tile + 3);
+  while (ns > 0 && !tile_fits<T, false>(r0, ns, lo, hi, sb)) {
+    --ns;
+    hi = __ldg(a.rowptr + r0 + ns);
   }
-  const TileLayout<T> L(r0, nrows, lo, hi);
-  if (threadIdx.x == 0) {
-    m->r0 = r0;
-    m->nrows = nrows;
-    m->lo = lo;
-    m->hi = hi;
-    m->fits = 1;
-    m->nlong = 0;
+  if (ns > 0) {
+    const TileLayout<T, false> L(r0, ns, lo, hi);
+    if (threadIdx.x == 0) {
+      m->r0 = r0;
+      m->nrows = nrows;
+      m->lo = lo;
+      m->hi = hi;
+      m->nstaged = ns;
+      m->nlong = 0;
+    }
+    T* sv = reinterpret_cast<T*>(smem);
+    int* sc = reinterpret_cast<int*>(smem + L.off_c());
+    int* sr = reinterpret_cast<int*>(smem + L.off_r());
+    for (int j = lo + threadIdx.x; j < hi; j += NT)
+      sv[j - L.lo_v] = __ldg(a.val + j);
+    for (int j = lo + threadIdx.x; j < hi; j += NT)
+      sc[j - L.lo_c] = __ldg(a.colind + j);
+    for (int r = r0 + threadIdx.x; r <= r0 + ns; r += NT)
+      sr[r - L.lo_r] = __ldg(a.rowptr + r);
+    __syncthreads();
+    walk_staged<T, SYM, LONG, false>(a, smem, m, threadIdx.x, NT, warp, NT / 32, lane, 1);
   }
-  T* sv = reinterpret_cast<T*>(smem);
-  int* sc = reinterpret_cast<int*>(smem + L.bytes_v);
-  int* sr = reinterpret_cast<int*>(smem + L.bytes_v + L.bytes_c);
-  for (int j = lo + threadIdx.x; j < hi; j += NT)
-    sv[j - L.lo_v] = __ldg(a.val + j);
-  for (int j = lo + threadIdx.x; j < hi; j += NT)
-    sc[j - L.lo_c] = __ldg(a.colind + j);
-  for (int r = r0 + threadIdx.x; r <= r1; r += NT)
-    sr[r - L.lo_r] = __ldg(a.rowptr + r);
-  __syncthreads();
-  walk_staged<T, SYM, LONG, false>(a, smem, m, threadIdx.x, NT, warp, NT / 32, lane, 1);
+  if (ns < nrows)
+    walk_direct<T, SYM, false>(a, r0 + ns, nrows - ns, warp, NT / 32, lane);
 }
 
 // Diagonal-only symmetric block (nnz == 0, rowptr == NULL): csr_matrix.cpp:85,
@@ -430,7 +588,8 @@ __global__ void scale_kernel(int n, T beta, T* __restrict__ y)
 // Plan kernels
 // ---------------------------------------------------------------------------
 __global__ void plan_tiles_kernel(const int32_t* __restrict__ rowptr, int rows, long long nnz,
-                                  int num_tiles, long long tile_bytes, int32_t* __restrict__ meta)
+                                  int num_tiles, long long tile_bytes, long long w_entry,
+                                  long long w_row, int32_t* __restrict__ meta)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > num_tiles)
@@ -441,10 +600,10 @@ __global__ void plan_tiles_kernel(const int32_t* __restrict__ rowptr, int rows, 
     return;
   }
   const long long target = (long long)b * tile_bytes;
-  int lo = 0, hi = rows; // smallest r with 12*rowptr[r] + 4*r >= target
+  int lo = 0, hi = rows; // smallest r with w_entry*rowptr[r] + w_row*r >= target
   while (lo < hi) {
     const int mid = lo + ((hi - lo) >> 1);
-    const long long g = 12ll * rowptr[mid] + 4ll * mid;
+    const long long g = w_entry * rowptr[mid] + w_row * mid;
     if (g >= target)
       hi = mid;
     else
@@ -499,7 +658,14 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   p->num_tiles = 0;
   if (p->nnz == 0 || p->rows == 0 || d_rowptr == nullptr)
     return B200_OK;
-  const long long total = 12ll * p->nnz + 4ll * p->rows;
+  // walk + storage decide what a row and an entry cost in the stage
+  p->w_entry = 12;
+  p->w_row = 4;
+  if (p->symmetric && p->walk == 1 && p->variant == 0) {
+    p->w_entry = 20; // value + column + product
+    p->w_row = 20;   // rowptr + diagonal + x
+  }
+  const long long total = (long long)p->w_entry * p->nnz + (long long)p->w_row * p->rows;
   const long long nt = (total + p->tile_bytes - 1) / p->tile_bytes;
   B200_REQUIRE(nt < (1ll << 30), "too many tiles");
   p->num_tiles = (int32_t)nt;
@@ -507,17 +673,37 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   const int threads = 256;
   const int blocks = (int)((nt + 1 + threads - 1) / threads);
   plan_tiles_kernel<<<blocks, threads, 0, st>>>(d_rowptr, p->rows, p->nnz, p->num_tiles,
-                                                p->tile_bytes, p->d_tile_meta);
+                                                p->tile_bytes, p->w_entry, p->w_row, p->d_tile_meta);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
+// Row walk for stencil-like rows (the chunked gathers keep ~16 loads in flight per
+// row; measured faster down to the 7-point stencil's mean of 7); stream walk when
+// rows are very short (mean < 5: a thread per row cannot keep the memory pipeline
+// full) and for symmetric storage (lower-triangle rows are short and the scatter
+// wants the staged x / diagonal slices): 7-point 256^3 symmetric 0.87 -> 0.25 ms.
+static void plan_choose_walk(Plan* p)
+{
+  if (p->walk_forced >= 0) {
+    p->walk = p->walk_forced;
+    return;
+  }
+  const double mean = p->rows > 0 ? (double)p->nnz / (double)p->rows : 0.0;
+  p->walk = (p->symmetric || mean < 5.0) ? 1 : 0;
+}
+
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant == 0 || variant == 1, "variant must be 0 or 1");
+  B200_REQUIRE(variant >= 0 && variant <= 3, "variant must be 0..3");
+  // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
+  // 2: pipeline, row walk forced; 3: pipeline, stream walk forced
+  p->walk_forced = variant == 2 ? 0 : (variant == 3 ? 1 : -1);
+  if (variant >= 2)
+    variant = 0;
   B200_REQUIRE(tile_bytes >= 1024 && tile_bytes + 2048 <= MAX_STAGE_BYTES, "tile_bytes out of range");
   B200_REQUIRE(stages >= 2 && stages <= 8, "stages out of range");
-  B200_REQUIRE(cw == 2 || cw == 4 || cw == 8, "consumer_warps must be 2, 4 or 8");
+  B200_REQUIRE(cw == 2 || cw == 4 || cw == 8 || cw == 16, "consumer_warps must be 2, 4, 8 or 16");
   B200_REQUIRE(ctas >= 1 && ctas <= 8, "ctas_per_sm out of range");
   p->variant = variant;
   p->tile_bytes = tile_bytes;
@@ -550,30 +736,40 @@ static int set_smem(Kernel k, size_t bytes, SmemCache& cache)
   return B200_OK;
 }
 
-template <typename T, bool SYM, bool DOT, bool LONG, int CW>
+template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 static int launch_pipe(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
   const size_t smem = pipe_smem_bytes(p);
   static SmemCache cache;
-  if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW>, smem, cache))
+  if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK>, smem, cache))
     return rc;
   const int grid = std::min<long long>(p.num_tiles, (long long)num_sms() * p.ctas_per_sm);
-  spmv_pipe_kernel<T, SYM, DOT, LONG, CW><<<grid, (CW + 1) * 32, smem, st>>>(a);
+  spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK><<<grid, (CW + 1) * 32, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-template <typename T, bool SYM, bool DOT, bool LONG>
+template <typename T, bool SYM, bool DOT, bool LONG, int WALK>
 static int launch_pipe_cw(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
   switch (p.consumer_warps) {
   case 2:
-    return launch_pipe<T, SYM, DOT, LONG, 2>(p, a, st);
+    return launch_pipe<T, SYM, DOT, LONG, 2, WALK>(p, a, st);
   case 4:
-    return launch_pipe<T, SYM, DOT, LONG, 4>(p, a, st);
+    return launch_pipe<T, SYM, DOT, LONG, 4, WALK>(p, a, st);
+  case 16:
+    return launch_pipe<T, SYM, DOT, LONG, 16, WALK>(p, a, st);
   default:
-    return launch_pipe<T, SYM, DOT, LONG, 8>(p, a, st);
+    return launch_pipe<T, SYM, DOT, LONG, 8, WALK>(p, a, st);
   }
+}
+
+template <typename T, bool SYM, bool DOT, bool LONG>
+static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
+{
+  if (p.walk == 1)
+    return launch_pipe_cw<T, SYM, DOT, LONG, 1>(p, a, st);
+  return launch_pipe_cw<T, SYM, DOT, LONG, 0>(p, a, st);
 }
 
 template <typename T, bool SYM, bool LONG>
@@ -655,18 +851,19 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.dot_out = d_dot;
 
   const bool has_long = p.max_row_len > SHORT_ROW;
-  const bool bulk_ok = aligned16(d_rowptr) && aligned16(d_colind) && aligned16(d_val);
+  const bool bulk_ok = aligned16(d_rowptr) && aligned16(d_colind) && aligned16(d_val)
+                       && (!(SYM && p.walk == 1) || (aligned16(d_diag) && aligned16(d_x)));
   if (p.variant == 0 && bulk_ok) {
     if (d_dot != nullptr) {
       B200_REQUIRE((std::is_same<T, double>::value) && !SYM, "dot epilogue: general fp64 only");
       B200_REQUIRE((long long)num_sms() * p.ctas_per_sm <= p.partials_len, "partials too small");
       if (has_long)
-        return launch_pipe_cw<T, SYM, !SYM, true>(p, a, st);
-      return launch_pipe_cw<T, SYM, !SYM, false>(p, a, st);
+        return launch_pipe_walk<T, SYM, !SYM, true>(p, a, st);
+      return launch_pipe_walk<T, SYM, !SYM, false>(p, a, st);
     }
     if (has_long)
-      return launch_pipe_cw<T, SYM, false, true>(p, a, st);
-    return launch_pipe_cw<T, SYM, false, false>(p, a, st);
+      return launch_pipe_walk<T, SYM, false, true>(p, a, st);
+    return launch_pipe_walk<T, SYM, false, false>(p, a, st);
   }
   B200_REQUIRE(d_dot == nullptr, "dot epilogue needs variant 0 and 16-byte aligned arrays");
   if (has_long)
@@ -708,11 +905,6 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
     return rc;
   }
   cudaStream_t st = as_stream(stream);
-  rc = plan_partition(p, d_rowptr, st);
-  if (rc) {
-    b200_csr_plan_destroy(p);
-    return rc;
-  }
   p->partials_len = num_sms() * 8;
   unsigned long long* d_hist = nullptr;
   int* d_max = nullptr;
@@ -732,7 +924,7 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   cudaMemsetAsync(p->d_counter, 0, sizeof(unsigned int), st);
   cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * 32, st);
   cudaMemsetAsync(d_max, 0, sizeof(int), st);
-  if (p->num_tiles > 0) {
+  if (nnz > 0 && rows > 0) {
     const int blocks = std::min((rows + 255) / 256, num_sms() * 8);
     plan_hist_kernel<<<blocks, 256, 0, st>>>(d_rowptr, rows, d_hist, d_max);
   }
@@ -749,6 +941,13 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   p->max_row_len = mx;
   cudaFree(d_hist);
   cudaFree(d_max);
+  d_hist = nullptr;
+  d_max = nullptr;
+  // the histogram picks the walk, the walk fixes the stage weights, the weights cut the tiles
+  plan_choose_walk(p);
+  rc = plan_partition(p, d_rowptr, st);
+  if (rc || cudaStreamSynchronize(st) != cudaSuccess)
+    return fail(rc ? rc : B200_ECUDA);
   *plan = p;
   return B200_OK;
 }
@@ -784,16 +983,14 @@ int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int til
 {
   B200_REQUIRE(plan != nullptr, "plan is NULL");
   Plan* p = static_cast<Plan*>(plan);
-  const int old_tile = p->tile_bytes;
   int rc = plan_apply_tuning(p, variant, tile_bytes, stages, consumer_warps, ctas_per_sm);
   if (rc)
     return rc;
-  if (tile_bytes != old_tile) {
-    rc = plan_partition(p, d_rowptr, as_stream(stream));
-    if (rc)
-      return rc;
-    B200_CUDA(cudaStreamSynchronize(as_stream(stream)));
-  }
+  plan_choose_walk(p);
+  rc = plan_partition(p, d_rowptr, as_stream(stream));
+  if (rc)
+    return rc;
+  B200_CUDA(cudaStreamSynchronize(as_stream(stream)));
   return B200_OK;
 }
 
