@@ -17,9 +17,48 @@ from spmv_b200 import kernels as K  # noqa: E402
 from spmv_b200 import synth  # noqa: E402
 
 
+def timeit(run, a):
+    for _ in range(a.warmup):
+        run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.iters):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / a.iters
+
+
+def powerlaw(a, dev):
+    """--n = rows (config 5 shape, scaled down); general CSR, one block."""
+    import numpy as np
+    N = a.n
+    rp, col, val = synth.powerlaw_rows(N, 0, N)
+    rp_d = torch.from_numpy(rp.astype(np.int32)).to(dev)
+    ci_d = torch.from_numpy(col.astype(np.int32)).to(dev)
+    v_d = torch.from_numpy(val).to(dev)
+    nnz = int(rp[-1])
+    plan = K.CsrPlan(N, N, rp_d, False, nnz=nnz)
+    x = torch.from_numpy(synth.bump_vector(N, 0, N)).to(dev)
+    y = torch.empty(N, dtype=torch.float64, device=dev)
+    nbytes = 12 * nnz + 4 * (N + 1) + 16 * N
+    ms = timeit(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y), a)
+    info = plan.info()
+    print(f"powerlaw rows={N} nnz={nnz} max_row={info['max_row_len']} tiles={info['num_tiles']} (plan defaults): "
+          f"{ms:.4f} ms  {nbytes / ms / 1e6:.1f} GB/s algorithmic", flush=True)
+    want = torch.sparse_csr_tensor(rp_d.long(), ci_d.long(), v_d, size=(N, N)).matmul(x)
+    print("  rel err vs torch.sparse:", float((y - want).norm() / want.norm()), flush=True)
+    for variant in (2, 3, 4):
+        for tb, cw, ct in ((24576, 8, 3), (24576, 16, 2), (49152, 8, 2), (49152, 16, 2), (32768, 8, 3)):
+            plan.tune(variant, tb, 2, cw, ct)
+            ms = timeit(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y), a)
+            print(f"  variant={variant} tile={tb} cw={cw} ctas={ct}: {ms:.4f} ms  {nbytes / ms / 1e6:.1f} GB/s", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--case", default="sym7", choices=["sym7", "sym27", "general7", "general27"])
+    ap.add_argument("--case", default="sym7", choices=["sym7", "sym27", "general7", "general27", "powerlaw"])
     ap.add_argument("--n", type=int, default=256)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
@@ -27,6 +66,8 @@ def main():
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     n = a.n
+    if a.case == "powerlaw":
+        return powerlaw(a, dev)
     N = n * n * n
     sym = a.case.startswith("sym")
     stencil = 7 if a.case.endswith("7") and not a.case.endswith("27") else 27

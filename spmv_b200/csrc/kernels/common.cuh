@@ -145,7 +145,14 @@ __device__ __forceinline__ T warp_sum(T v)
 }
 
 // Fire-and-forget global add (SASS RED.E.ADD.F64 / .F32).
+// (B200_EXPERIMENT_NO_RED: timing experiments only -- wrong results -- to read the
+// in-situ cost of the scatter off a kernel that otherwise does the same work.)
+#ifdef B200_EXPERIMENT_NO_RED
+__device__ __forceinline__ void red_add(double* addr, double v) { if (v == 1.2345e300) *addr = v; }
+__device__ __forceinline__ void red_add(float* addr, float v) { if (v == 1.2345e30f) *addr = v; }
+#else
 __device__ __forceinline__ void red_add(double* addr, double v) { atomicAdd(addr, v); }
 __device__ __forceinline__ void red_add(float* addr, float v) { atomicAdd(addr, v); }
+#endif
 
 } // namespace b200

@@ -43,10 +43,9 @@
 namespace b200
 {
 
-#ifndef B200_WALK_CHUNK
-#define B200_WALK_CHUNK 16
-#endif
-constexpr int WALK_CHUNK = B200_WALK_CHUNK;
+// Walks (template parameter WALK): one thread per row fetching 16 / 8 / 4 entries
+// at a time, or the two-phase stream walk.
+constexpr int WALK_ROW16 = 0, WALK_STREAM = 1, WALK_ROW8 = 2, WALK_ROW4 = 3;
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
 constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
 constexpr int MAX_STAGE_BYTES = 96 * 1024;
@@ -83,10 +82,13 @@ struct SpmvArgs {
 
 __host__ __device__ __forceinline__ int round16(int b) { return (b + 15) & ~15; }
 
-// Byte layout of one staged tile: [values | colind | rowptr] and, for the extended
-// (symmetric stream) layout, [diag | x | products]; each loaded slice starts at the
-// 16-byte aligned global element at or below the tile's first element.
-template <typename T, bool EXT>
+// Byte layout of one staged tile: [values | colind | rowptr], then for LAY >= 1
+// the tile's slices of [diag | x] (symmetric storage) and for LAY == 2 a region
+// for the stream walk's products; each loaded slice starts at the 16-byte aligned
+// global element at or below the tile's first element.
+constexpr int LAY_PLAIN = 0, LAY_DX = 1, LAY_DXP = 2;
+
+template <typename T, int LAY>
 struct TileLayout {
   int lo_v, lo_c, lo_r, lo_d;
   int bytes_v, bytes_c, bytes_r, bytes_d, bytes_p;
@@ -100,8 +102,8 @@ struct TileLayout {
     bytes_v = round16((hi - lo_v) * (int)sizeof(T));
     bytes_c = round16((hi - lo_c) * 4);
     bytes_r = round16((r0 + nrows + 1 - lo_r) * 4);
-    bytes_d = EXT ? round16((r0 + nrows - lo_d) * (int)sizeof(T)) : 0;
-    bytes_p = EXT ? round16((hi - lo) * (int)sizeof(T)) : 0;
+    bytes_d = LAY >= LAY_DX ? round16((r0 + nrows - lo_d) * (int)sizeof(T)) : 0;
+    bytes_p = LAY == LAY_DXP ? round16((hi - lo) * (int)sizeof(T)) : 0;
   }
   __host__ __device__ int off_c() const { return bytes_v; }
   __host__ __device__ int off_r() const { return bytes_v + bytes_c; }
@@ -114,14 +116,14 @@ struct TileLayout {
 
 // 64-bit pre-check first: a tile holding one enormous row must not overflow the
 // int byte counts of TileLayout.
-template <typename T, bool EXT>
+template <typename T, int LAY>
 __host__ __device__ __forceinline__ bool tile_fits(int r0, int nrows, int lo, int hi, int sb)
 {
-  const long long per_entry = (long long)sizeof(T) + 4 + (EXT ? (long long)sizeof(T) : 0);
-  const long long per_row = 4 + (EXT ? 2ll * (long long)sizeof(T) : 0);
+  const long long per_entry = (long long)sizeof(T) + 4 + (LAY == LAY_DXP ? (long long)sizeof(T) : 0);
+  const long long per_row = 4 + (LAY >= LAY_DX ? 2ll * (long long)sizeof(T) : 0);
   if ((long long)(hi - lo) * per_entry + per_row * nrows > (long long)sb)
     return false;
-  return TileLayout<T, EXT>(r0, nrows, lo, hi).total() <= sb;
+  return TileLayout<T, LAY>(r0, nrows, lo, hi).total() <= sb;
 }
 
 // ---------------------------------------------------------------------------
@@ -164,18 +166,25 @@ __device__ __forceinline__ T store_row(const SpmvArgs<T>& a, int r, T sum)
   return out;
 }
 
-// Walk a tile that sits in shared memory.  Returns this thread's share of
-// sum_i x[i]*y[i] over the tile's rows (general storage only).
-template <typename T, bool SYM, bool LONG, bool DOT>
+// Walk a tile that sits in shared memory, one thread per row.  Returns this
+// thread's share of sum_i x[i]*y[i] over the tile's rows (general storage only).
+// CHUNK entries of a row are fetched together (16 for stencil-length rows, 8 / 4
+// for short ones: fewer predicated-off slots).  LAY_DX: the tile's diagonal and x
+// slices are staged too, and gathers that fall on the tile's own rows read the
+// staged x.
+template <typename T, bool SYM, bool LONG, bool DOT, int CHUNK, int LAY>
 __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsigned char* stage,
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
 {
+  constexpr bool DX = LAY >= LAY_DX;
   const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
-  const TileLayout<T, false> L(r0, nrows, lo, hi);
+  const TileLayout<T, LAY> L(r0, nrows, lo, hi);
   const T* sv = reinterpret_cast<const T*>(stage);
   const int* sc = reinterpret_cast<const int*>(stage + L.off_c());
   const int* sr = reinterpret_cast<const int*>(stage + L.off_r());
+  const T* sd = reinterpret_cast<const T*>(stage + L.off_d()) + (r0 - L.lo_d); // diag[r0 + k]
+  const T* sx = reinterpret_cast<const T*>(stage + L.off_x()) + (r0 - L.lo_d); // x[r0 + k]
   double dot = 0.0;
 
   for (int k = tid; k < nrows; k += nthreads) {
@@ -189,26 +198,30 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
     }
     T xi = 0, sum = 0;
     if (SYM) {
-      xi = __ldg(a.x + r);
-      sum = mul_rn(__ldg(a.diag + r), xi);
+      xi = DX ? sx[k] : __ldg(a.x + r);
+      sum = mul_rn(DX ? sd[k] : __ldg(a.diag + r), xi);
     }
-    // Chunks of WALK_CHUNK entries: all column indices, values and x gathers of a
-    // chunk are issued before the first add, so one row keeps up to WALK_CHUNK
+    // Chunks of CHUNK entries: all column indices, values and x gathers of a
+    // chunk are issued before the first add, so one row keeps up to CHUNK
     // independent L2-latency gathers in flight; the adds then run in j order.
-    for (int base = rs; base < re; base += WALK_CHUNK) {
-      int c[WALK_CHUNK];
-      T v[WALK_CHUNK], xv[WALK_CHUNK];
+    for (int base = rs; base < re; base += CHUNK) {
+      int c[CHUNK];
+      T v[CHUNK], xv[CHUNK];
 #pragma unroll
-      for (int u = 0; u < WALK_CHUNK; ++u) {
+      for (int u = 0; u < CHUNK; ++u) {
         const bool ok = base + u < re;
-        c[u] = ok ? sc[base + u - L.lo_c] : 0;
+        c[u] = ok ? sc[base + u - L.lo_c] : (DX ? r0 : 0);
         v[u] = ok ? sv[base + u - L.lo_v] : T(0);
       }
 #pragma unroll
-      for (int u = 0; u < WALK_CHUNK; ++u)
-        xv[u] = (base + u < re) ? __ldg(a.x + c[u]) : T(0);
+      for (int u = 0; u < CHUNK; ++u) {
+        if (DX && (unsigned)(c[u] - r0) < (unsigned)nrows)
+          xv[u] = sx[c[u] - r0];
+        else
+          xv[u] = (base + u < re) ? __ldg(a.x + c[u]) : T(0);
+      }
 #pragma unroll
-      for (int u = 0; u < WALK_CHUNK; ++u) {
+      for (int u = 0; u < CHUNK; ++u) {
         if (base + u < re) {
           sum = add_rn(sum, mul_rn(v[u], xv[u]));
           if (SYM)
@@ -254,10 +267,11 @@ __device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned cha
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
 {
+  constexpr int LAY = SYM ? LAY_DXP : LAY_PLAIN;
   constexpr bool EXT = SYM;
   constexpr int U = 4;
   const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
-  const TileLayout<T, EXT> L(r0, nrows, lo, hi);
+  const TileLayout<T, LAY> L(r0, nrows, lo, hi);
   T* sv = reinterpret_cast<T*>(stage) + (lo - L.lo_v);                  // sv[j - lo]
   const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c);
   const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r); // sr[k]
@@ -407,7 +421,7 @@ __device__ __forceinline__ void grid_dot_reduce(double v, int tid, int nthreads,
 // ---------------------------------------------------------------------------
 // Variant 0: persistent CTAs, bulk-async staged ring, warp-specialised.
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
-//   WALK 0: one thread per row (chunked gathers);  WALK 1: two-phase stream walk.
+//   WALK_ROW16/8/4: one thread per row (chunked gathers);  WALK_STREAM: two-phase stream walk.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem()
 {
@@ -417,7 +431,8 @@ __device__ __forceinline__ void fence_proxy_async_smem()
 template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
-  constexpr bool EXT = SYM && WALK == 1;
+  constexpr int LAY = SYM ? (WALK == WALK_STREAM ? LAY_DXP : LAY_DX) : LAY_PLAIN;
+  constexpr int CHUNK = WALK == WALK_ROW4 ? 4 : (WALK == WALK_ROW8 ? 8 : 16);
   extern __shared__ __align__(128) unsigned char smem[];
   const int stages = a.stages;
   const int sb = a.stage_bytes;
@@ -454,7 +469,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
         // Stage the longest prefix of rows that fits: a tile overshoots its byte
         // budget by at most its last row, so this drops one (long) row at most.
         int ns = nrows, hi = t1.y;
-        while (ns > 0 && !tile_fits<T, EXT>(r0, ns, lo, hi, sb)) {
+        while (ns > 0 && !tile_fits<T, LAY>(r0, ns, lo, hi, sb)) {
           --ns;
           hi = __ldg(a.rowptr + r0 + ns);
         }
@@ -466,7 +481,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
         m->nstaged = ns;
         m->nlong = 0;
         if (ns > 0) {
-          const TileLayout<T, EXT> L(r0, ns, lo, hi);
+          const TileLayout<T, LAY> L(r0, ns, lo, hi);
           unsigned char* dst = smem + (size_t)s * sb;
           mbar_arrive_expect_tx(full + s, (uint32_t)L.loaded());
           if (L.bytes_v > 0)
@@ -474,7 +489,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
           if (L.bytes_c > 0)
             bulk_g2s(dst + L.off_c(), a.colind + L.lo_c, L.bytes_c, full + s);
           bulk_g2s(dst + L.off_r(), a.rowptr + L.lo_r, L.bytes_r, full + s);
-          if (EXT) {
+          if (LAY >= LAY_DX) {
             bulk_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
             bulk_g2s(dst + L.off_x(), a.x + L.lo_d, L.bytes_d, full + s);
           }
@@ -493,13 +508,13 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
     StageMeta* m = meta + s;
     const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
     if (ns > 0) {
-      if (WALK == 1) {
+      if (WALK == WALK_STREAM) {
         dot += walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp,
                                               CW, lane, 1);
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
       } else {
-        dot += walk_staged<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp,
-                                              CW, lane, 1);
+        dot += walk_staged<T, SYM, LONG, DOT, CHUNK, LAY>(a, smem + (size_t)s * sb, m, threadIdx.x,
+                                                          CW * 32, warp, CW, lane, 1);
       }
     }
     if (ns < nrows)
@@ -531,12 +546,12 @@ __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
     return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int ns = nrows, hi = __ldg(a.tile_meta + 2 * tile + 3);
-  while (ns > 0 && !tile_fits<T, false>(r0, ns, lo, hi, sb)) {
+  while (ns > 0 && !tile_fits<T, LAY_PLAIN>(r0, ns, lo, hi, sb)) {
     --ns;
     hi = __ldg(a.rowptr + r0 + ns);
   }
   if (ns > 0) {
-    const TileLayout<T, false> L(r0, ns, lo, hi);
+    const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
     if (threadIdx.x == 0) {
       m->r0 = r0;
       m->nrows = nrows;
@@ -555,7 +570,7 @@ __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
     for (int r = r0 + threadIdx.x; r <= r0 + ns; r += NT)
       sr[r - L.lo_r] = __ldg(a.rowptr + r);
     __syncthreads();
-    walk_staged<T, SYM, LONG, false>(a, smem, m, threadIdx.x, NT, warp, NT / 32, lane, 1);
+    walk_staged<T, SYM, LONG, false, 16, LAY_PLAIN>(a, smem, m, threadIdx.x, NT, warp, NT / 32, lane, 1);
   }
   if (ns < nrows)
     walk_direct<T, SYM, false>(a, r0 + ns, nrows - ns, warp, NT / 32, lane);
@@ -661,9 +676,10 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   // walk + storage decide what a row and an entry cost in the stage
   p->w_entry = 12;
   p->w_row = 4;
-  if (p->symmetric && p->walk == 1 && p->variant == 0) {
-    p->w_entry = 20; // value + column + product
-    p->w_row = 20;   // rowptr + diagonal + x
+  if (p->symmetric && p->variant == 0) {
+    p->w_row = 20; // rowptr + diagonal + x
+    if (p->walk == WALK_STREAM)
+      p->w_entry = 20; // value + column + product
   }
   const long long total = (long long)p->w_entry * p->nnz + (long long)p->w_row * p->rows;
   const long long nt = (total + p->tile_bytes - 1) / p->tile_bytes;
@@ -678,11 +694,14 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   return B200_OK;
 }
 
-// Row walk for stencil-like rows (the chunked gathers keep ~16 loads in flight per
-// row; measured faster down to the 7-point stencil's mean of 7); stream walk when
-// rows are very short (mean < 5: a thread per row cannot keep the memory pipeline
-// full) and for symmetric storage (lower-triangle rows are short and the scatter
-// wants the staged x / diagonal slices): 7-point 256^3 symmetric 0.87 -> 0.25 ms.
+// The row-length histogram picks the walk (sweeps in profiles/r01_walk_sweeps.md):
+//   general storage: 16-entry chunks for stencil-length rows (27-point: mean 26.8),
+//     8-entry chunks when the mean is <= 10 (7-point: 0.306 -> 0.292 ms);
+//   symmetric storage (lower-triangle rows are short): 4-entry chunks up to a mean of
+//     4 (7-point lower: mean 3; 0.87 -> 0.23 ms), else 8-entry chunks (27-point lower:
+//     mean 12.9; 1.49 -> 0.69 ms);
+//   irregular rows (longest row > 16x the mean, e.g. power-law): the stream walk,
+//     whose entry-parallel phase does not care how the entries fall into rows.
 static void plan_choose_walk(Plan* p)
 {
   if (p->walk_forced >= 0) {
@@ -690,20 +709,43 @@ static void plan_choose_walk(Plan* p)
     return;
   }
   const double mean = p->rows > 0 ? (double)p->nnz / (double)p->rows : 0.0;
-  p->walk = (p->symmetric || mean < 5.0) ? 1 : 0;
+  if (p->max_row_len > SHORT_ROW && (double)p->max_row_len > 16.0 * mean)
+    p->walk = WALK_STREAM;
+  else if (p->symmetric)
+    p->walk = mean <= 4.0 ? WALK_ROW4 : WALK_ROW8;
+  else
+    p->walk = mean <= 10.0 ? WALK_ROW8 : WALK_ROW16;
+}
+
+// Launch shape that measured best for each walk (tile bytes, consumer warps, CTAs/SM).
+static void plan_default_shape(const Plan* p, int* tile_bytes, int* cw, int* ctas)
+{
+  switch (p->walk) {
+  case WALK_ROW4:
+    *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
+    break;
+  case WALK_ROW8:
+    *tile_bytes = 24 * 1024, *cw = 8, *ctas = p->symmetric ? 3 : 4;
+    break;
+  case WALK_STREAM:
+    *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
+    break;
+  default:
+    *tile_bytes = 48 * 1024, *cw = 8, *ctas = 2;
+  }
 }
 
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant >= 0 && variant <= 3, "variant must be 0..3");
+  B200_REQUIRE(variant >= 0 && variant <= 5, "variant must be 0..5");
   // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
-  // 2: pipeline, row walk forced; 3: pipeline, stream walk forced
-  p->walk_forced = variant == 2 ? 0 : (variant == 3 ? 1 : -1);
+  // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4
+  p->walk_forced = variant >= 2 ? variant - 2 : -1;
   if (variant >= 2)
     variant = 0;
   B200_REQUIRE(tile_bytes >= 1024 && tile_bytes + 2048 <= MAX_STAGE_BYTES, "tile_bytes out of range");
   B200_REQUIRE(stages >= 2 && stages <= 8, "stages out of range");
-  B200_REQUIRE(cw == 2 || cw == 4 || cw == 8 || cw == 16, "consumer_warps must be 2, 4, 8 or 16");
+  B200_REQUIRE(cw == 4 || cw == 8 || cw == 16, "consumer_warps must be 4, 8 or 16");
   B200_REQUIRE(ctas >= 1 && ctas <= 8, "ctas_per_sm out of range");
   p->variant = variant;
   p->tile_bytes = tile_bytes;
@@ -753,8 +795,6 @@ template <typename T, bool SYM, bool DOT, bool LONG, int WALK>
 static int launch_pipe_cw(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
   switch (p.consumer_warps) {
-  case 2:
-    return launch_pipe<T, SYM, DOT, LONG, 2, WALK>(p, a, st);
   case 4:
     return launch_pipe<T, SYM, DOT, LONG, 4, WALK>(p, a, st);
   case 16:
@@ -767,9 +807,16 @@ static int launch_pipe_cw(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 template <typename T, bool SYM, bool DOT, bool LONG>
 static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
-  if (p.walk == 1)
-    return launch_pipe_cw<T, SYM, DOT, LONG, 1>(p, a, st);
-  return launch_pipe_cw<T, SYM, DOT, LONG, 0>(p, a, st);
+  switch (p.walk) {
+  case WALK_STREAM:
+    return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
+  case WALK_ROW8:
+    return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW8>(p, a, st);
+  case WALK_ROW4:
+    return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW4>(p, a, st);
+  default:
+    return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW16>(p, a, st);
+  }
 }
 
 template <typename T, bool SYM, bool LONG>
@@ -852,7 +899,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
 
   const bool has_long = p.max_row_len > SHORT_ROW;
   const bool bulk_ok = aligned16(d_rowptr) && aligned16(d_colind) && aligned16(d_val)
-                       && (!(SYM && p.walk == 1) || (aligned16(d_diag) && aligned16(d_x)));
+                       && (!SYM || (aligned16(d_diag) && aligned16(d_x)));
   if (p.variant == 0 && bulk_ok) {
     if (d_dot != nullptr) {
       B200_REQUIRE((std::is_same<T, double>::value) && !SYM, "dot epilogue: general fp64 only");
@@ -896,14 +943,7 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   p->cols = cols;
   p->nnz = nnz;
   p->symmetric = symmetric ? 1 : 0;
-  int rc = plan_apply_tuning(p, env_int("B200_SPMV_VARIANT", 0),
-                             env_int("B200_SPMV_TILE_BYTES", 48 * 1024),
-                             env_int("B200_SPMV_STAGES", 2), env_int("B200_SPMV_CWARPS", 8),
-                             env_int("B200_SPMV_CTAS", 2));
-  if (rc) {
-    delete p;
-    return rc;
-  }
+  int rc = B200_OK;
   cudaStream_t st = as_stream(stream);
   p->partials_len = num_sms() * 8;
   unsigned long long* d_hist = nullptr;
@@ -943,8 +983,18 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   cudaFree(d_max);
   d_hist = nullptr;
   d_max = nullptr;
-  // the histogram picks the walk, the walk fixes the stage weights, the weights cut the tiles
+  // the histogram picks the walk and its launch shape (environment overrides for
+  // sweeps), the walk fixes the stage weights, the weights cut the tiles
+  const int variant = env_int("B200_SPMV_VARIANT", 0);
+  p->walk_forced = variant >= 2 ? variant - 2 : -1;
   plan_choose_walk(p);
+  int d_tile, d_cw, d_ctas;
+  plan_default_shape(p, &d_tile, &d_cw, &d_ctas);
+  rc = plan_apply_tuning(p, variant, env_int("B200_SPMV_TILE_BYTES", d_tile),
+                         env_int("B200_SPMV_STAGES", 2), env_int("B200_SPMV_CWARPS", d_cw),
+                         env_int("B200_SPMV_CTAS", d_ctas));
+  if (rc)
+    return fail(rc);
   rc = plan_partition(p, d_rowptr, st);
   if (rc || cudaStreamSynchronize(st) != cudaSuccess)
     return fail(rc ? rc : B200_ECUDA);
