@@ -58,6 +58,14 @@ public:
   Matrix(const HostCSR<T>& mat_local, const HostCSR<T>& mat_remote, const std::vector<T>& mat_diagonal,
          std::shared_ptr<spmv::L2GMap> col_map, std::shared_ptr<spmv::L2GMap> row_map, int nnz_full,
          std::shared_ptr<DeviceExecutor> exec);
+  /// Device-side builders: wrap blocks that already live in executor
+  /// memory (e.g. generated or split on the GPU) without a host round trip.  `remote`
+  /// may be null for a single-block operator; `nnz` is what non_zeros() reports for
+  /// symmetric storage (Matrix.cpp:56-59).  Same contract checks as the three
+  /// host constructors.
+  static Matrix<T> from_blocks(std::unique_ptr<SubMatrix<T>> local, std::unique_ptr<SubMatrix<T>> remote,
+                               std::shared_ptr<spmv::L2GMap> col_map, std::shared_ptr<spmv::L2GMap> row_map,
+                               std::int64_t nnz, bool symmetric, std::shared_ptr<DeviceExecutor> exec);
   ~Matrix();
   Matrix(Matrix&&) noexcept;
   Matrix& operator=(Matrix&&) noexcept;
@@ -97,6 +105,7 @@ public:
                                   CommunicationModel cm = CommunicationModel::collective_blocking);
 
 private:
+  Matrix() = default;
   void spmv(T* x, T* y) const;
   void spmv_overlap(T* x, T* y) const;
   void spmv_sym(T* x, T* y) const;

@@ -18,6 +18,12 @@ public:
   CSRMatrix(std::shared_ptr<DeviceExecutor> exec, int32_t num_rows, int32_t num_cols,
             int64_t num_non_zeros, const int32_t* rowptr, const int32_t* colind, const T* values,
             const T* diagonal = nullptr, bool symmetric = false);
+  /// Adopt arrays that already live in `exec` memory (allocated with exec->alloc; the
+  /// block frees them).  rowptr/colind/values must be null when num_non_zeros == 0.
+  struct adopt_t {};
+  CSRMatrix(adopt_t, std::shared_ptr<DeviceExecutor> exec, int32_t num_rows, int32_t num_cols,
+            int64_t num_non_zeros, int32_t* d_rowptr, int32_t* d_colind, T* d_values,
+            T* d_diagonal = nullptr, bool symmetric = false);
   ~CSRMatrix() override;
   CSRMatrix(const CSRMatrix&) = delete;
   CSRMatrix& operator=(const CSRMatrix&) = delete;

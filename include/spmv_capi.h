@@ -61,6 +61,9 @@ SPMVH_API int spmvh_matrix_create(void** mat, void* exec, const int32_t* rowptr,
                                   int64_t num_col_ghosts, int symmetric, int cm);
 SPMVH_API int spmvh_matrix_read_petsc(void** mat, void* exec, const char* filename, int symmetric, int cm);
 SPMVH_API int spmvh_matrix_create_A(void** mat, void* exec, int N);
+/* Device-side builder of the 7-/27-point Laplacian (demos/CreateLaplace3D.h); exec must be B200. */
+SPMVH_API int spmvh_matrix_create_laplace3d(void** mat, void* exec, int nx, int ny, int64_t nz_global, int stencil,
+                                            int symmetric, int cm);
 SPMVH_API int spmvh_matrix_destroy(void* mat);
 /* out: rows, cols, non_zeros, symmetric, format_size, has_remote_block, local nnz, remote nnz */
 SPMVH_API int spmvh_matrix_info(void* mat, int64_t out[8]);

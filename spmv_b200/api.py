@@ -50,6 +50,7 @@ _SIG = {
     "spmvh_matrix_create": [_pp, _p, _p, _p, _p, _i64, _i64, _p, _i64, _p, _i64, _int, _int],
     "spmvh_matrix_read_petsc": [_pp, _p, C.c_char_p, _int, _int],
     "spmvh_matrix_create_A": [_pp, _p, _int],
+    "spmvh_matrix_create_laplace3d": [_pp, _p, _int, _int, _i64, _int, _int, _int],
     "spmvh_matrix_destroy": [_p],
     "spmvh_matrix_info": [_p, C.POINTER(_i64)],
     "spmvh_matrix_col_map": [_p, _pp],
@@ -476,6 +477,15 @@ def write_petsc_binary_vector(filename, values):
 def create_A(N, exec):
     h = C.c_void_p()
     _ck(host_lib().spmvh_matrix_create_A(C.byref(h), exec.h, int(N)))
+    return Matrix(h, exec)
+
+
+def create_laplace3d(exec, nx, ny, nz_global, stencil, symmetric=False, cm=COLLECTIVE_BLOCKING):
+    """demos/CreateLaplace3D.h: the 7-/27-point operator generated straight into executor memory
+    (plane split by owner_ranges over the world's ranks); exec must be a B200Executor."""
+    h = C.c_void_p()
+    _ck(host_lib().spmvh_matrix_create_laplace3d(C.byref(h), exec.h, int(nx), int(ny), int(nz_global), int(stencil),
+                                                 int(bool(symmetric)), int(cm)))
     return Matrix(h, exec)
 
 

@@ -63,6 +63,30 @@ Matrix<T>::Matrix(const HostCSR<T>& mat_local, const HostCSR<T>& mat_remote,
 }
 //-----------------------------------------------------------------------------
 template <typename T>
+Matrix<T> Matrix<T>::from_blocks(std::unique_ptr<SubMatrix<T>> local, std::unique_ptr<SubMatrix<T>> remote,
+                                 std::shared_ptr<spmv::L2GMap> col_map, std::shared_ptr<spmv::L2GMap> row_map,
+                                 std::int64_t nnz, bool symmetric, std::shared_ptr<DeviceExecutor> exec)
+{
+  if (!local)
+    throw std::runtime_error("Matrix::from_blocks: the local block is required");
+  if (symmetric && !remote)
+    throw std::runtime_error("Matrix::from_blocks: symmetric storage carries a remote block (Matrix.cpp:63-71)");
+  if (!symmetric && !remote && col_map->overlapping())
+    throw std::runtime_error("Ovelapping not supported in this format!");
+  if (!symmetric && remote && !col_map->overlapping())
+    throw std::runtime_error("Ovelapping not enabled in column mapping!");
+  Matrix<T> m;
+  m._exec = exec;
+  m._mat_local = std::move(local);
+  m._mat_remote = std::move(remote);
+  m._col_map = col_map;
+  m._row_map = row_map;
+  m._nnz = static_cast<int>(nnz);
+  m._symmetric = symmetric;
+  return m;
+}
+//-----------------------------------------------------------------------------
+template <typename T>
 Matrix<T>::~Matrix() = default;
 template <typename T>
 Matrix<T>::Matrix(Matrix&&) noexcept = default;

@@ -2,6 +2,7 @@
 #include "spmv_capi.h"
 
 #include "../../../demos/CreateA.h"
+#include "../../../demos/CreateLaplace3D.h"
 #include "host_util.h"
 #include <spmv/spmv.h>
 
@@ -217,6 +218,14 @@ int spmvh_matrix_read_petsc(void** mat, void* exec, const char* filename, int sy
 int spmvh_matrix_create_A(void** mat, void* exec, int N)
 {
   return guarded([&] { *mat = new Matrix<double>(create_A(MPI_COMM_WORLD, N, as_exec(exec))); });
+}
+int spmvh_matrix_create_laplace3d(void** mat, void* exec, int nx, int ny, int64_t nz_global, int stencil,
+                                  int symmetric, int cm)
+{
+  return guarded([&] {
+    *mat = new Matrix<double>(
+        create_laplace3d(MPI_COMM_WORLD, as_exec(exec), nx, ny, nz_global, stencil, symmetric != 0, as_cm(cm)));
+  });
 }
 int spmvh_matrix_destroy(void* mat)
 {

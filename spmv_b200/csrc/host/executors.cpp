@@ -365,6 +365,27 @@ CSRMatrix<T>::CSRMatrix(std::shared_ptr<DeviceExecutor> exec, int32_t num_rows, 
 }
 
 template <typename T>
+CSRMatrix<T>::CSRMatrix(adopt_t, std::shared_ptr<DeviceExecutor> exec, int32_t num_rows, int32_t num_cols,
+                        int64_t num_non_zeros, int32_t* d_rowptr, int32_t* d_colind, T* d_values,
+                        T* d_diagonal, bool symmetric)
+{
+  if (num_non_zeros == 0 && (d_rowptr || d_colind || d_values))
+    throw std::runtime_error("CSRMatrix: an empty block carries no arrays (csr_matrix.cpp:35)");
+  if (num_non_zeros > 0 && !(d_rowptr && d_colind && d_values))
+    throw std::runtime_error("CSRMatrix: null array in a non-empty block");
+  this->_exec = exec;
+  this->_num_rows = num_rows;
+  this->_num_cols = num_cols;
+  this->_num_non_zeros = num_non_zeros;
+  this->_symmetric = symmetric;
+  _rowptr = d_rowptr;
+  _colind = d_colind;
+  _values = d_values;
+  this->_diagonal = d_diagonal;
+  exec->spmv_init(_op, *this);
+}
+
+template <typename T>
 CSRMatrix<T>::~CSRMatrix()
 {
   this->_exec->spmv_finalize(_op);

@@ -132,6 +132,26 @@ def main():
                     check(err < 1e-7, tag + f": cg x rel err {err}")
             A.close()
 
+    # device-side builder (demos/CreateLaplace3D.h) against create_matrix on host-generated rows
+    if mode == "gpu":
+        nx, ny, nz = 6, 5, 8 * size if size not in (1, 2, 4, 8) else 8
+        for st in (7, 27):
+            N, rows = cases.make_problem("lap7" if st == 7 else "lap27", (nx, ny, nz))
+            for sym, cm in combos:
+                tag = f"create_laplace3d st={st} size={size} sym={sym} cm={cm}"
+                inp = cases.local_inputs(rows, N, rank, size)
+                A0 = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                              inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
+                A1 = api.create_laplace3d(ex, nx, ny, nz, st, sym, cm)
+                check(cases.same_plan(A1.col_map().plan(), A0.col_map().plan()), tag + ": column map differs")
+                check(cases.same_plan(A1.row_map().plan(), A0.row_map().plan()), tag + ": row map differs")
+                check(cases.same_block(A1.local_block(), A0.local_block()), tag + ": local block differs")
+                check(cases.same_block(A1.remote_block(), A0.remote_block()), tag + ": remote block differs")
+                check(A1.non_zeros() == A0.non_zeros() and A1.rows() == A0.rows() and A1.cols() == A0.cols(),
+                      tag + ": sizes differ")
+                A0.close()
+                A1.close()
+
     # read_petsc + create_A builders over the multi-process transport
     N, rows = cases.make_problem("powerlaw", 3000)
     rp, col, val = rows(0, N)
