@@ -1,14 +1,15 @@
 #!/usr/bin/env python
-"""bench.py -- the headline measurement (contract in the task prompt).
+"""bench.py -- the headline measurement (contract in the task statement).
 
-Workload (config.workload): distributed fp64 general-CSR SpMV, one halo update +
-one Matrix::mult per step, on the 27-point 3-D Laplacian with 256x256x256 rows per
-GPU (weak scaling: the grid is 256 x 256 x 256*N, 1-D slab partition).  That is the
-case BASELINE.json's target is quoted on (>=70 % of the HBM roofline at 1 GPU).
-metric = aggregate algorithmic GB/s (SURVEY.md section 8d formula).
+Workload (config.workload) = BASELINE.json configs[1]: symmetric-storage fp64 CSR SpMV on
+the 3-D 7-point Laplacian, 256^3 rows per GPU (weak scaling over z-slabs: the grid is
+256 x 256 x 256*N).  One step = L2GMap::update + Matrix::mult, called through the
+reference-shaped API (spmv_b200.api -> libspmv_b200.so -> the C ABI of libb200spmv.so).
+metric = aggregate algorithmic GB/s (SURVEY.md 8d byte formulas).
 
-Extra numbers ride in "also": symmetric-storage 7-point SpMV (config 2) and CG
-iterations/s (configs 3/4 shape, 27-point 256^3 per GPU).
+"also" carries the other BASELINE configs that fit this run: general 27-point SpMV (the
+case the >=70 % roofline target is quoted on), CG iterations/s and the CG solve to
+rtol 1e-8 on the 27-point operator (configs 3/4 shape), each with its own roofline figure.
 """
 import argparse
 import json
@@ -23,7 +24,7 @@ sys.path.insert(0, ROOT)
 
 NX = NY = 256
 NZ_PER_GPU = 256
-STENCIL = 27
+CPU_SAMPLE_NZ = 64  # planes of the CPU legs' slab (1/4 of the 1-GPU workload)
 
 
 def parse():
@@ -34,7 +35,6 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nz", type=int, default=NZ_PER_GPU, help="z-planes per GPU (default 256)")
     ap.add_argument("--no-extras", action="store_true", help="skip the 'also' measurements and cpu_baseline")
-    ap.add_argument("--sweep", action="store_true", help="kernel tuning sweep (prints a table, no JSON)")
     return ap.parse_args()
 
 
@@ -97,64 +97,50 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def algorithmic_bytes(nnz, rows, cols_touched):
-    """General CSR SpMV, SURVEY.md 8d: 12*nnz + 4*(rows+1) + 8*cols_touched + 8*rows."""
-    return 12 * nnz + 4 * (rows + 1) + 8 * cols_touched + 8 * rows
+# ----------------------------------------------------------------------------
+# algorithmic bytes (x counted once, y written once)
+# ----------------------------------------------------------------------------
+def bytes_general(nnz_local, nnz_remote, rows, ncols, two_blocks):
+    b = 12 * nnz_local + 4 * (rows + 1) + 8 * ncols + 8 * rows
+    if two_blocks:
+        b += 12 * nnz_remote + 4 * (rows + 1)
+    return b
+
+
+def bytes_symmetric(nnz_lower, nnz_remote, rows, nghosts):
+    b = 12 * nnz_lower + 4 * (rows + 1) + 24 * rows
+    if nnz_remote:
+        b += 12 * nnz_remote + 4 * (rows + 1) + 8 * nghosts
+    return b
 
 
 # ----------------------------------------------------------------------------
-# the B200 arm
+# the B200 arm: everything through the reference-shaped API (spmv_b200.api)
 # ----------------------------------------------------------------------------
-class SlabOperator:
-    """One rank's share of the Laplacian on a 1-D slab partition, with the halo plan the
-    reference's L2GMap would build for it (L2GMap.cpp:346-479): neighbours ascending by
-    rank, ghosts landing in the tail of x, no unpack step (L2GMap.cpp:586-598)."""
+class Operator:
+    """One rank's spmv::Matrix of the slab-partitioned Laplacian plus its vectors."""
 
-    def __init__(self, rank, size, nx, ny, nz, stencil, dev, nccl_comm, symmetric=False):
+    def __init__(self, api, ex, dev, rank, size, nz, stencil, symmetric):
         import torch
-        from spmv_b200 import kernels as K
-
-        self.K, self.torch = K, torch
-        self.rank, self.size, self.dev, self.comm = rank, size, dev, nccl_comm
-        z0, z1, nzg = rank * nz, (rank + 1) * nz, size * nz
-        plane = nx * ny
-        self.rows = plane * nz
-        self.symmetric = symmetric
-        mode = 1 if symmetric else (0 if size == 1 else 2)
-        g = K.laplace3d(nx, ny, nzg, z0, z1, stencil, mode, dev)
-        self.nghosts = g["nghosts"]
+        from spmv_b200 import synth
+        self.api, self.ex, self.torch = api, ex, torch
+        self.symmetric, self.stencil, self.size = symmetric, stencil, size
+        # overlap schedule (local block while the halo is in flight) whenever there are neighbours
+        cm = api.P2P_NONBLOCKING if size > 1 else api.P2P_BLOCKING
+        self.A = api.create_laplace3d(ex, NX, NY, nz * size, stencil, symmetric, cm)
+        info = self.A._info()
+        self.rows, self.nnz_local, self.nnz_remote = info[0], info[6], info[7]
+        self.two_blocks = bool(info[5])
+        self.col_map = self.A.col_map()
+        self.nghosts = self.col_map.num_ghosts()
         self.ncols = self.rows + self.nghosts
-        self.local, self.remote, self.diag = g["local"], g["remote"], g["diag"]
-        self.nnz_local = int(self.local[0][-1].item())
-        self.nnz_remote = int(self.remote[0][-1].item()) if self.remote is not None else 0
-        self.plan_local = K.CsrPlan(self.rows, self.ncols, self.local[0], symmetric, nnz=self.nnz_local)
-        self.plan_remote = (K.CsrPlan(self.rows, self.ncols, self.remote[0], False, nnz=self.nnz_remote)
-                            if self.remote is not None and self.nnz_remote > 0 else None)
-        # halo plan
-        nbr, sidx, scnt, rcnt = [], [], [], []
-        if rank > 0:
-            nbr.append(rank - 1)
-            sidx.append(torch.arange(0, plane, dtype=torch.int32))
-            scnt.append(plane)
-            rcnt.append(plane)
-        if rank < size - 1:
-            nbr.append(rank + 1)
-            sidx.append(torch.arange(self.rows - plane, self.rows, dtype=torch.int32))
-            scnt.append(plane)
-            rcnt.append(plane)
-        import numpy as np
-        self.nnbr = len(nbr)
-        self.nbr = np.array(nbr, dtype=np.int32)
-        self.send_cnt = np.array(scnt, dtype=np.int32)
-        self.send_off = np.concatenate([[0], np.cumsum(scnt)[:-1]]).astype(np.int32) if nbr else np.zeros(0, np.int32)
-        self.recv_cnt = np.array(rcnt, dtype=np.int32)
-        self.recv_off = (self.rows + np.concatenate([[0], np.cumsum(rcnt)[:-1]])).astype(np.int32) if nbr else np.zeros(0, np.int32)
-        self.indexbuf = torch.cat(sidx).to(dev) if nbr else None
-        self.sendbuf = torch.empty(int(sum(scnt)), dtype=torch.float64, device=dev) if nbr else None
-        self.comm_stream = torch.cuda.Stream(device=dev) if nbr else None
-        self.ev_packed = torch.cuda.Event()
-        self.ev_arrived = torch.cuda.Event()
-        self.launches_per_step = (1 if self.nnbr == 0 else 2) + (1 if self.plan_remote else 0) + (1 if symmetric else 0)
+        self.nnbr = len(self.col_map.get("neighbours")) if size > 1 else 0
+        n_glob = self.rows * size
+        self.x = torch.zeros(self.ncols, dtype=torch.float64, device=dev)
+        self.x[: self.rows] = torch.from_numpy(synth.bump_vector(n_glob, rank * self.rows, (rank + 1) * self.rows)).to(dev)
+        self.y = torch.empty(self.rows, dtype=torch.float64, device=dev)
+        # our kernels per step: pack (if neighbours) + local block + remote block (if it has entries)
+        self.launches_per_step = (1 if self.nnbr else 0) + 1 + (1 if self.nnz_remote > 0 else 0)
 
     def nnz_full(self):
         if self.symmetric:
@@ -162,70 +148,26 @@ class SlabOperator:
         return self.nnz_local + self.nnz_remote
 
     def algorithmic_bytes(self):
-        if self.symmetric:  # 12*nnz_lower + 4*(rows+1) + 3*8*rows (+ remote block)
-            b = 12 * self.nnz_local + 4 * (self.rows + 1) + 24 * self.rows
-            if self.nnz_remote:
-                b += 12 * self.nnz_remote + 4 * (self.rows + 1) + 8 * self.nghosts
-            return b
-        b = algorithmic_bytes(self.nnz_local, self.rows, self.ncols)
-        if self.nnz_remote:
-            b += 12 * self.nnz_remote + 4 * (self.rows + 1)
-        return b
+        if self.symmetric:
+            return bytes_symmetric(self.nnz_local, self.nnz_remote, self.rows, self.nghosts)
+        return bytes_general(self.nnz_local, self.nnz_remote, self.rows, self.ncols, self.two_blocks)
 
-    def update(self, x):
-        """L2GMap::update (p2p_nonblocking flavour): pack, then grouped send/recv on a side stream."""
-        if self.nnbr == 0:
-            return
-        import ctypes as C
-        from spmv_b200 import check, lib
-        torch, K = self.torch, self.K
-        K.gather(self.indexbuf, x, self.sendbuf)
-        main = torch.cuda.current_stream()
-        self.ev_packed.record(main)
-        self.comm_stream.wait_event(self.ev_packed)
-        p = lambda a: a.ctypes.data_as(C.c_void_p)
-        check(lib().b200_halo_exchange(self.comm, self.nnbr, p(self.nbr), C.c_void_p(self.sendbuf.data_ptr()),
-                                       p(self.send_cnt), p(self.send_off), C.c_void_p(x.data_ptr()),
-                                       p(self.recv_cnt), p(self.recv_off), 8,
-                                       C.c_void_p(self.comm_stream.cuda_stream)))
-        self.ev_arrived.record(self.comm_stream)
+    def local_kernel_bytes(self):
+        """Algorithmic bytes of the dominant launch (the local block)."""
+        if self.symmetric:
+            return bytes_symmetric(self.nnz_local, 0, self.rows, 0)
+        return bytes_general(self.nnz_local, 0, self.rows, self.rows if self.two_blocks else self.ncols, False)
 
-    def mult(self, x, y, dot=None, kernel_events=None):
-        """Matrix::mult: spmv / spmv_overlap / spmv_sym(_overlap) schedules (Matrix.cpp:483-552)."""
-        torch, K = self.torch, self.K
+    def step(self, kernel_events=None):
+        self.col_map.update(self.x)  # L2GMap::update (demos/spmv.cpp:88)
         if kernel_events is not None:
             kernel_events[0].record()
-        if self.symmetric:
-            K.symv(self.plan_local, *self.local, self.diag, x, y)
-        elif dot is not None and self.plan_remote is None:
-            K.spmv_dot(self.plan_local, *self.local, x, y, dot)
-        else:
-            K.spmv(self.plan_local, *self.local, x, y)
+        self.A.mult(self.x, self.y)  # Matrix::mult   (demos/spmv.cpp:93)
         if kernel_events is not None:
             kernel_events[1].record()
-        if self.nnbr:
-            torch.cuda.current_stream().wait_event(self.ev_arrived)  # update_finalise
-        if self.plan_remote is not None:
-            K.spmv(self.plan_remote, *self.remote, x, y, 1.0, 1.0)
 
-
-def make_nccl_comm(rank, size, dev):
-    """Our own NCCL communicator (ids travel over torch.distributed)."""
-    import ctypes as C
-    import torch
-    import torch.distributed as dist
-    from spmv_b200 import check, lib
-    if size == 1:
-        return None
-    buf = C.create_string_buffer(128)
-    if rank == 0:
-        check(lib().b200_nccl_unique_id(buf))
-    t = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev)
-    dist.broadcast(t, 0)
-    raw = bytes(t.cpu().tolist())
-    comm = C.c_void_p()
-    check(lib().b200_nccl_comm_create(C.byref(comm), size, rank, raw))
-    return comm
+    def close(self):
+        self.A.close()
 
 
 class Timer:
@@ -257,294 +199,269 @@ class Timer:
         return ms
 
 
-def cg_iteration_factory(op, size, dev):
-    """One CG iteration (cg.cpp:55-86) as fused kernels; returns (iterate, state, launches)."""
-    import ctypes as C
+def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
+    """Timed loop of update+mult; returns dict with step time, kernel time, optional e2e."""
     import torch
-    from spmv_b200 import check, lib
-    from spmv_b200 import kernels as K
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    # >= 10 untimed steps: the first exchanges also set up NCCL's peer connections (milliseconds)
+    for _ in range(max(warmup, 10 if op.size > 1 else 3)):
+        op.step()
+    ms = timer.run(lambda i: op.step(kev[i]), steps)
+    ms_step = ms / steps
+    kern = sorted(a.elapsed_time(b) for a, b in kev)
+    kern_avg = sum(kern) / len(kern)
+    out = {"ms_per_step": ms_step, "kernel_ms_avg": kern_avg, "kernel_ms_min": kern[0],
+           "kernel_ms_median": kern[len(kern) // 2],
+           "GBps": op.algorithmic_bytes() * op.size / (ms_step * 1e-3) / 1e9,
+           "GFLOPs": 2 * op.nnz_full() * op.size / (ms_step * 1e-3) / 1e9,
+           "kernel_GBps": op.local_kernel_bytes() / (kern_avg * 1e-3) / 1e9}
+    out["frac_of_hbm_peak"] = out["kernel_GBps"] / peak
+    if with_e2e:
+        # host buffers: H2D of x and D2H of y inside the timed region, through the executor's
+        # copy_from / copy_to (DeviceExecutor::copy_from, device_executor.h:60-66)
+        M = op.rows
+        xh = torch.empty(M, dtype=torch.float64).pin_memory()
+        xh.copy_(op.x[:M].cpu())
+        yh = torch.empty(M, dtype=torch.float64).pin_memory()
+        xh_np, yh_np = xh.numpy(), yh.numpy()
+
+        def e2e_step(_i):
+            op.ex.copy_from_host(op.x, xh_np)
+            op.step()
+            op.ex.copy_to_host(yh_np, op.y)
+
+        n = max(3, min(steps, 10))
+        for i in range(3):
+            e2e_step(i)
+        ms_e2e = timer.run(e2e_step, n) / n
+        out["e2e"] = {"value": op.algorithmic_bytes() * op.size / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s",
+                      "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M}
+    return out
+
+
+def measure_cg(api, op, timer, dev, size):
+    """CG on `op` (b = A*1, x0 = 0): iterations/s over a fixed 100 iterations, then the solve
+    to rtol 1e-8 (BASELINE config 3: kmax 5000) with its iteration count and final residual."""
+    import torch
     M = op.rows
-    ones = torch.ones(op.ncols, dtype=torch.float64, device=dev)
+    ones = torch.zeros(op.ncols, dtype=torch.float64, device=dev)
+    ones[:M] = 1.0
     b = torch.empty(M, dtype=torch.float64, device=dev)
-    op.update(ones)
-    op.mult(ones, b)  # b = A*1 (SURVEY 8d config 3)
-    p = torch.zeros(op.ncols, dtype=torch.float64, device=dev)
-    p[:M] = b
-    r, x, Ap = b.clone(), torch.zeros(M, dtype=torch.float64, device=dev), torch.empty(M, dtype=torch.float64, device=dev)
-    st, scratch = K.new_cg_state(dev), K.new_dot_scratch(dev)
-    rr = torch.zeros(1, dtype=torch.float64, device=dev)
-    K.dot(r, r, rr, scratch)
-    sp = lambda t: C.c_void_p(t.data_ptr())
-    cur = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    if size > 1:
-        check(lib().b200_allreduce_sum_f64(op.comm, sp(rr), 1, cur()))
-    K.cg_init_state(st, rr, 1e-30, 1 << 30)  # never converges inside the timed window
-    fused = op.plan_remote is None and not op.symmetric
-    pM = p[:M]
+    op.col_map.update(ones)
+    op.A.mult(ones, b)
+    xs = torch.zeros(M, dtype=torch.float64, device=dev)
+    api.cg(op.ex, op.A, b, xs, 10, 0.0)  # warm-up
+    iters = 100
+    ms = timer.run(lambda i: api.cg(op.ex, op.A, b, xs, iters, 0.0), 1)
+    res = {"iters_per_s": iters / (ms * 1e-3), "ms_per_iter": ms / iters, "rows_per_gpu": M,
+           "algorithmic_GBps": (op.algorithmic_bytes() + 11 * 8 * M) * size / (ms / iters * 1e-3) / 1e9,
+           "note": "100 iterations through spmv::cg incl. its setup (allocations, r0 norm)"}
+    holder = {}
 
-    def iterate(_i=0):
-        op.update(p)
-        if fused:
-            op.mult(p, Ap, dot=st[1:2])
-        else:
-            op.mult(p, Ap)
-            K.dot(pM, Ap, st[1:2], scratch, st[4:5])
-        if size > 1:
-            check(lib().b200_allreduce_sum_f64(op.comm, sp(st[1:2]), 1, cur()))
-        K.cg_update_xr(M, st, pM, Ap, x, r)
-        if size > 1:
-            check(lib().b200_allreduce_sum_f64(op.comm, sp(st[2:3]), 1, cur()))
-        K.cg_update_p(M, st, r, pM)
+    def solve(_i):
+        holder["it"], holder["hist"] = api.cg(op.ex, op.A, b, xs, 5000, 1e-8, history=True)
 
-    launches = op.launches_per_step + (0 if fused else 1) + 2
-    return iterate, st, launches
+    ms = timer.run(solve, 1)
+    hist = holder["hist"]
+    res["solve_rtol_1e-8"] = {"iterations": int(holder["it"]), "ms": ms,
+                              "iters_per_s": holder["it"] / (ms * 1e-3) if ms > 0 else None,
+                              "final_rel_residual": float(hist[-1] / (b.norm().item() if size == 1 else 1.0))
+                              if len(hist) and size == 1 else None}
+    return res
 
 
 def run_b200(args):
-    import numpy as np
     import torch
-    from spmv_b200 import kernels as K
-    from spmv_b200 import synth
+    from spmv_b200 import api
 
     rank = int(os.environ.get("RANK", "0"))
     size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    assert size == args.gpus or size == 1 and args.gpus == 1, f"--gpus {args.gpus} but WORLD_SIZE={size}"
+    assert size == args.gpus or (size == 1 and args.gpus == 1), f"--gpus {args.gpus} but WORLD_SIZE={size}"
     assert torch.cuda.is_available(), "bench.py needs a GPU: there is no CPU path"
     dev = torch.device(f"cuda:{local_rank}")
     torch.cuda.set_device(dev)
     if size > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    comm = make_nccl_comm(rank, size, dev)
+        # setup collectives of the host layer (ranges, ghost counts, index lists) ride on gloo;
+        # the data path (halo payload, CG scalars) is NCCL inside libb200spmv.so
+        api.init_world_from_torch(dist.new_group(backend="gloo"))
+    ex = api.B200Executor.create(local_rank)
+    ex.use_torch_stream()
     timer = Timer(size, dev)
+    peak, peak_src = peak_hbm()
     nz = args.nz
 
-    op = SlabOperator(rank, size, NX, NY, nz, STENCIL, dev, comm)
-    if args.sweep:
-        return sweep(op, dev, args)
-    M, N_glob = op.rows, op.rows * size
-    x = torch.zeros(op.ncols, dtype=torch.float64, device=dev)
-    x[:M] = torch.from_numpy(synth.bump_vector(N_glob, rank * M, (rank + 1) * M)).to(dev)
-    y = torch.empty(M, dtype=torch.float64, device=dev)
-
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-
-    def step(i):
-        op.update(x)
-        op.mult(x, y, kernel_events=kev[i] if i < len(kev) else None)
-
-    for i in range(max(args.warmup, 3)):
-        step(10 ** 9)
+    # ---- headline: BASELINE configs[1], symmetric-storage 7-point SpMV -------------------
+    op = Operator(api, ex, dev, rank, size, nz, 7, True)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    ms = timer.run(step, args.steps)
-    # keep the GPU busy a little longer so the 100 ms sampler sees the loaded clocks
-    if rank == 0:
-        t_end = time.time() + 1.0
-        while time.time() < t_end:
-            for i in range(20):
-                step(10 ** 9)
-            torch.cuda.synchronize()
-        clocks = sampler.stop()
-    ms_step = ms / args.steps
-    bytes_rank = op.algorithmic_bytes()
-    value = bytes_rank * size / (ms_step * 1e-3) / 1e9
-    kern_ms = sorted(a.elapsed_time(b) for a, b in kev)
-    kern_avg = sum(kern_ms) / len(kern_ms)
-    kern_bytes = algorithmic_bytes(op.nnz_local, op.rows, op.rows if size > 1 else op.ncols)
-    peak, peak_src = peak_hbm()
-    achieved = kern_bytes / (kern_avg * 1e-3) / 1e9
-
-    # ---- e2e: host buffers, H2D of x and D2H of y inside the timed region -------------
-    xh = torch.empty(M, dtype=torch.float64).pin_memory()
-    xh.copy_(x[:M].cpu())
-    yh = torch.empty(M, dtype=torch.float64).pin_memory()
-
-    def e2e_step(i):
-        x[:M].copy_(xh, non_blocking=True)
-        op.update(x)
-        op.mult(x, y)
-        yh.copy_(y, non_blocking=True)
-
-    e2e_steps = max(3, min(args.steps, 10))
-    for i in range(3):
-        e2e_step(i)
-    ms_e2e = timer.run(e2e_step, e2e_steps) / e2e_steps
-    e2e = {"value": bytes_rank * size / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms_e2e,
-           "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M}
+    head = measure_spmv(op, timer, args.steps, args.warmup, peak, with_e2e=True)
+    # keep the GPUs busy ~1 s longer so the 100 ms sampler sees the loaded clocks (same count on
+    # every rank: the step time is already the max over ranks)
+    for _ in range(int(min(1000.0 / max(head["ms_per_step"], 1e-3), 20000))):
+        op.step()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    head_launches = op.launches_per_step * args.steps
+    cfg = {"workload": f"BASELINE configs[1]: symmetric-storage fp64 CSR SpMV (L2GMap::update + Matrix::mult), 3-D "
+                       f"7-point Laplacian {NX}x{NY}x{nz} rows per GPU, 1-D slab partition over z",
+           "rows_per_gpu": op.rows, "stored_nnz_per_gpu": op.nnz_local + op.nnz_remote, "nnz_full_per_gpu": op.nnz_full(),
+           "n_gpus": size, "api": "spmv_b200.api (create_laplace3d, L2GMap.update, Matrix.mult) -> libspmv_b200.so -> C ABI",
+           "l2": "inputs (1.07 GB streamed per step, x and y 134 MB each) exceed the 126 MB L2; no explicit flush",
+           "GFLOPs": head["GFLOPs"]}
+    op.close()
+    del op
 
     also = {}
     if not args.no_extras:
-        # CG iterations/s on the same operator (configs 3/4 shape)
-        iterate, st, cg_launches = cg_iteration_factory(op, size, dev)
-        for i in range(3):
-            iterate()
-        cg_steps = 20
-        ms_cg = timer.run(iterate, cg_steps) / cg_steps
-        also["cg_27pt"] = {"iters_per_s": 1e3 / ms_cg, "ms_per_iter": ms_cg, "rows_per_gpu": M,
-                           "gpu_launches_per_iter": cg_launches,
-                           "algorithmic_GBps": (bytes_rank + 11 * 8 * M) * size / (ms_cg * 1e-3) / 1e9}
-        del iterate, st
-        # symmetric-storage 7-point SpMV (config 2)
-        ops = SlabOperator(rank, size, NX, NY, nz, 7, dev, comm, symmetric=True)
-        ys = torch.empty(M, dtype=torch.float64, device=dev)
-
-        def sstep(i):
-            ops.update(x)
-            ops.mult(x, ys)
-
-        for i in range(3):
-            sstep(i)
-        ms_s = timer.run(sstep, 20) / 20
-        sb = ops.algorithmic_bytes()
-        also["sym_7pt"] = {"GBps": sb * size / (ms_s * 1e-3) / 1e9, "ms_per_step": ms_s,
-                           "GFLOPs": 2 * ops.nnz_full() * size / (ms_s * 1e-3) / 1e9,
-                           "frac_of_hbm_peak": sb / (ms_s * 1e-3) / 1e9 / peak}
+        # ---- general 27-point SpMV (the case the roofline target is quoted on) -----------
+        op27 = Operator(api, ex, dev, rank, size, nz, 27, False)
+        g = measure_spmv(op27, timer, 30, 5, peak, with_e2e=True)
+        also["general_27pt_spmv"] = {"GBps": g["GBps"], "ms_per_step": g["ms_per_step"], "GFLOPs": g["GFLOPs"],
+                                     "kernel_ms_avg": g["kernel_ms_avg"], "kernel_ms_min": g["kernel_ms_min"],
+                                     "kernel_ms_median": g["kernel_ms_median"], "kernel_GBps": g["kernel_GBps"],
+                                     "frac_of_hbm_peak": g["frac_of_hbm_peak"], "e2e": g["e2e"],
+                                     "algorithmic_bytes_per_gpu": op27.algorithmic_bytes()}
+        # ---- CG on the 27-point operator (configs 3/4 shape) -----------------------------
+        also["cg_27pt"] = measure_cg(api, op27, timer, dev, size)
+        op27.close()
+        del op27
+        # ---- CG on the symmetric-storage 7-point operator --------------------------------
+        ops = Operator(api, ex, dev, rank, size, nz, 7, True)
+        also["cg_sym_7pt"] = measure_cg(api, ops, timer, dev, size)
+        ops.close()
         del ops
 
     if rank != 0:
         return
     line = {
-        "metric": "spmv_algorithmic_GBps", "value": value, "unit": "GB/s", "n_gpus": size, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"general CSR SpMV (halo update + Matrix::mult), 27-point Laplacian "
-                               f"{NX}x{NY}x{nz} rows per GPU, 1-D slab partition",
-                   "rows_per_gpu": M, "nnz_per_gpu": op.nnz_local + op.nnz_remote, "n_gpus": size,
-                   "l2": "inputs (5.7 GB matrix stream per step) far exceed the 126 MB L2; no explicit flush",
-                   "GFLOPs": 2 * (op.nnz_local + op.nnz_remote) * size / (ms_step * 1e-3) / 1e9},
-        "e2e": e2e,
-        "gpu_launches": op.launches_per_step * args.steps,
-        "clocks": clocks,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "spmv_pipe_kernel<double> (local block)",
-                     "kernel_ms_avg": kern_avg, "kernel_ms_min": kern_ms[0], "algorithmic_bytes": kern_bytes,
-                     "peak_source": peak_src, "frac_of_8TBps_nominal": achieved / 8000.0},
+        "metric": "spmv_algorithmic_GBps", "value": head["GBps"], "unit": "GB/s", "n_gpus": size, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "e2e": head["e2e"],
+        "gpu_launches": head_launches, "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",
+                     "frac": head["frac_of_hbm_peak"], "traffic": TRAFFIC_NCU.get("sym7"),
+                     "kernel": "spmv_pipe_kernel<double, SYM, ROW4> (local block; the event pair also spans the "
+                               "zero-fill of y that precedes it)",
+                     "kernel_ms_avg": head["kernel_ms_avg"], "kernel_ms_min": head["kernel_ms_min"],
+                     "algorithmic_bytes": bytes_symmetric(cfg["stored_nnz_per_gpu"] if size == 1 else 0, 0,
+                                                          cfg["rows_per_gpu"], 0) if size == 1 else None,
+                     "peak_source": peak_src, "frac_of_8TBps_nominal": head["kernel_GBps"] / 8000.0},
         "also": also,
     }
     if size == 1 and not args.no_extras:
-        line["cpu_baseline"] = cpu_baseline(sample_nz=32)
-    print(json.dumps(line), flush=True)
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
+# (profiles/): filled in when a capture of the current kernel exists, else null.
+TRAFFIC_NCU = {"sym7": None}
 
 
 # ----------------------------------------------------------------------------
-# CPU legs: the reference's own OpenMP kernel (oracle/_ref), all host threads
+# CPU legs: the reference's own OpenMP kernel (oracle/_ref), all host threads, on a slab of
+# the same operator (symmetric-storage 7-point)
 # ----------------------------------------------------------------------------
+def _split_lower(rp, col, val, rows):
+    """Strictly-lower triangle + diagonal of a square block with sorted rows (Matrix.cpp:337-349)."""
+    import numpy as np
+    r = np.repeat(np.arange(rows, dtype=np.int64), np.diff(rp))
+    low = col < r
+    diag = np.zeros(rows)
+    d = col == r
+    diag[r[d]] = val[d]
+    rp_l = np.zeros(rows + 1, dtype=np.int64)
+    np.cumsum(np.bincount(r[low], minlength=rows), out=rp_l[1:])
+    return rp_l.astype(np.int32), col[low].astype(np.int32), val[low].copy(), diag
+
+
 def _cpu_operator(sample_nz):
     import numpy as np
     from oracle import kernels as OK
     from spmv_b200 import synth
-    rp, col, val = synth.laplace3d_rows(NX, NY, sample_nz, 0, sample_nz, STENCIL)
+    rp, col, val = synth.laplace3d_rows(NX, NY, sample_nz, 0, sample_nz, 7)
     rows = len(rp) - 1
+    rp_l, ci_l, v_l, diag = _split_lower(rp, col, val, rows)
     cores = os.cpu_count() or 1
     if OK.have_ref():
-        op = OK.RefOmp(rows, rows, rp, col, val, threads=cores)
+        op = OK.RefOmp(rows, rows, rp_l, ci_l, v_l, diagonal=diag, symmetric=True, threads=cores)
         kind = "reference"
-        run = lambda x, y: op.run(x, y)
+        run = lambda x, y: op.run(x, y)  # noqa: E731
     else:  # the plain-C port, one thread
-        rp32, c32 = rp.astype(np.int32), col.astype(np.int32)
         kind, cores = "port", 1
-        run = lambda x, y: OK.lib().oracle_csr_spmv_f64(rows, rp32, c32, val, 1.0, x, 0.0, y)
+
+        def run(x, y):
+            y[:] = OK.symv(rp_l, ci_l, v_l, diag, x)
     x = synth.bump_vector(rows, 0, rows)
     y = np.zeros(rows)
-    nbytes = algorithmic_bytes(int(rp[-1]), rows, rows)
+    nbytes = bytes_symmetric(len(v_l), 0, rows, 0)
     return run, x, y, nbytes, kind, cores, rows
 
 
-def cpu_baseline(sample_nz=32, budget_s=10.0):
-    run, x, y, nbytes, kind, cores, rows = _cpu_operator(sample_nz)
+def _cpu_sample_text(rows, kind, cores, n):
+    return (f"symmetric-storage 7-point Laplacian {NX}x{NY}x{CPU_SAMPLE_NZ} slab ({rows} rows, "
+            f"1/{NZ_PER_GPU // CPU_SAMPLE_NZ} of the 1-GPU workload; GB/s is size-independent), {n} SpMVs, "
+            + (f"reference openmp/csr_kernels.openmp.cpp symmetric kernel, OMP_NUM_THREADS={cores}"
+               if kind == "reference" else "oracle C port, 1 thread"))
+
+
+def cpu_baseline(budget_s=12.0):
+    run, x, y, nbytes, kind, cores, rows = _cpu_operator(CPU_SAMPLE_NZ)
     run(x, y)
     t0, n = time.perf_counter(), 0
     while True:
         run(x, y)
         n += 1
         dt = time.perf_counter() - t0
-        if dt > budget_s or n >= 200:
+        if dt > budget_s or n >= 300:
             break
     return {"value": nbytes * n / dt / 1e9, "unit": "GB/s", "cores": cores, "kind": kind,
-            "ms_per_spmv": dt / n * 1e3,
-            "sample": f"27-point Laplacian {NX}x{NY}x{sample_nz} ({rows} rows, 1/{NZ_PER_GPU // sample_nz} of the "
-                      f"1-GPU workload), general CSR, {n} SpMVs, "
-                      + ("reference openmp/csr_kernels.openmp.cpp" if kind == "reference" else "oracle C port")}
+            "ms_per_spmv": dt / n * 1e3, "sample": _cpu_sample_text(rows, kind, cores, n)}
 
 
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    sample_nz = 32
-    run, x, y, nbytes, kind, cores, rows = _cpu_operator(sample_nz)
+    run, x, y, nbytes, kind, cores, rows = _cpu_operator(CPU_SAMPLE_NZ)
     for _ in range(max(args.warmup, 1)):
         run(x, y)
-    steps = min(args.steps, 50)
+    steps = min(args.steps, 100)
     t0 = time.perf_counter()
     for _ in range(steps):
         run(x, y)
     dt = time.perf_counter() - t0
     v = nbytes * steps / dt / 1e9
-    sample = (f"each step = one SpMV on a 27-point Laplacian {NX}x{NY}x{sample_nz} slab ({rows} rows; the GPU arm "
-              f"runs {NZ_PER_GPU} planes per GPU), GB/s is size-independent; "
-              + ("reference openmp/csr_kernels.openmp.cpp, OMP_NUM_THREADS=%d" % cores if kind == "reference"
-                 else "oracle C port, 1 thread"))
     print(json.dumps({
         "impl": "reference", "metric": "spmv_algorithmic_GBps", "value": v, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "general CSR SpMV, 27-point Laplacian, CPU sample", "rows": rows},
-        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
+        "config": {"workload": "BASELINE configs[1]: symmetric-storage fp64 CSR SpMV, 3-D 7-point Laplacian; each step = "
+                               "one SpMV of the reference's CPU kernel on a bounded slab of the operator",
+                   "rows": rows},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cores, "kind": kind,
+                         "sample": _cpu_sample_text(rows, kind, cores, steps)},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
 
-# ----------------------------------------------------------------------------
-# tuning sweep (one gpurun call explores the kernel's launch shape)
-# ----------------------------------------------------------------------------
-def sweep(op, dev, args):
-    import itertools
-    import torch
-    from spmv_b200 import synth
-    M = op.rows
-    x = torch.zeros(op.ncols, dtype=torch.float64, device=dev)
-    x[:M] = torch.from_numpy(synth.bump_vector(M, 0, M)).to(dev)
-    y = torch.empty(M, dtype=torch.float64, device=dev)
-    nbytes = op.algorithmic_bytes()
-    peak, _ = peak_hbm()
-    rows = []
-    grid = [(0, tb, st, cw, ct) for tb in (16384, 24576, 32768, 49152, 65536) for st in (2, 3, 4)
-            for cw in (2, 4, 8) for ct in (1, 2, 3, 4)]
-    grid += [(1, tb, 2, 4, 1) for tb in (8192, 16384, 32768, 49152)]
-    for variant, tb, st, cw, ct in grid:
-        smem = st * (tb + 2048 + 1056) + 16 * st + 256
-        if variant == 0 and smem * ct > 227 * 1024:
-            continue
-        try:
-            op.plan_local.tune(variant, tb, st, cw, ct)
-            for _ in range(3):
-                op.mult(x, y)
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(10):
-                op.mult(x, y)
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / 10
-        except Exception as e:  # noqa: BLE001
-            print(f"variant={variant} tile={tb} stages={st} cw={cw} ctas={ct}: {e}", flush=True)
-            continue
-        rows.append((ms, variant, tb, st, cw, ct))
-        print(f"variant={variant} tile={tb:6d} stages={st} cw={cw} ctas={ct}: {ms:.4f} ms "
-              f"{nbytes / ms / 1e6:8.1f} GB/s  {nbytes / ms / 1e6 / peak:.3f} of peak", flush=True)
-    rows.sort()
-    print("BEST:", rows[:5], flush=True)
+_JSON_OUT = sys.stdout
 
 
 def main():
+    global _JSON_OUT
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
+    # stdout carries exactly one JSON line: anything a library prints to fd 1 (NCCL's version
+    # banner, for one) goes to stderr instead
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     run_b200(args)
     try:
         import torch.distributed as dist

@@ -53,6 +53,9 @@ B200_API int b200_memcpy_d2h_async(void* h_dst, const void* d_src, size_t num_by
 B200_API int b200_host_alloc_pinned(void** h_ptr, size_t num_bytes);
 B200_API int b200_host_free_pinned(void* h_ptr);
 B200_API int b200_stream_create(void** stream);
+/* high != 0: greatest priority the device offers (the halo stream: its small copies and flag
+ * operations should never queue behind a resident SpMV kernel's work). */
+B200_API int b200_stream_create_priority(void** stream, int high);
 B200_API int b200_stream_destroy(void* stream);
 B200_API int b200_stream_synchronize(void* stream); /* DeviceExecutor::synchronize (device_executor.h:82) */
 B200_API int b200_event_create(void** event, int timing);
@@ -139,6 +142,24 @@ B200_API int b200_halo_exchange(void* comm, int nnbr, const int32_t* nbr_rank, c
                        void* comm_stream);
 /* In-stream sum-allreduce of n doubles (MPI_Allreduce at cg.cpp:49,65,75). */
 B200_API int b200_allreduce_sum_f64(void* comm, double* d_inout, int32_t n, void* stream);
+
+/* ---- direct peer halo over NVLink (the reference's one-sided models, L2GMap.cpp:645-721,
+ *      re-thought for one process per GPU): a rank's receive staging buffer is exported with
+ *      CUDA IPC, neighbours map it and push their packed slices into it with copy-engine
+ *      copies; arrival is signalled by a stream-ordered 32-bit flag write into the peer and
+ *      awaited with a stream-ordered wait -- no SM is used on either side and the host never
+ *      blocks.  (An NCCL send/recv kernel needs SM resources that a persistent SpMV kernel
+ *      holds for its whole run, so it cannot overlap with it reliably.)
+ *      b200_ipc_alloc: cudaMalloc + zero + export.  b200_ipc_open maps a peer's buffer (fails
+ *      for a handle created by this same process).  Flags are 4-byte aligned device words. ---- */
+#define B200_IPC_HANDLE_BYTES 64
+B200_API int b200_ipc_alloc(void** d_ptr, size_t num_bytes, char handle[B200_IPC_HANDLE_BYTES]);
+B200_API int b200_ipc_open(void** d_peer_ptr, const char handle[B200_IPC_HANDLE_BYTES]);
+B200_API int b200_ipc_close(void* d_peer_ptr);
+/* *d_flag = value, in stream order after everything enqueued before it. */
+B200_API int b200_stream_write_u32(void* stream, void* d_flag, uint32_t value);
+/* The stream does not proceed until *d_flag >= value (wrap-around compare, driver semantics). */
+B200_API int b200_stream_wait_u32_geq(void* stream, void* d_flag, uint32_t value);
 
 /* ---- CG building blocks: cg.cpp:47-85 (cblas_ddot/daxpy/dscal) and the
  *      scalar kernels of cuda/cg.cuda.cu:14-38, fused.  All scalars live in a

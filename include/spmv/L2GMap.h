@@ -103,6 +103,23 @@ private:
   mutable size_t _send_buf_bytes = 0;
   mutable void* _recv_buf = nullptr; // reverse_update staging
   mutable size_t _recv_buf_bytes = 0;
+
+  // ---- direct peer halo (b200spmv.h "direct peer halo") ----------------
+  // My staging buffer: [slot 0 | slot 1 | arrival flags, one uint32 per rank]; neighbours
+  // push their slices into the slot of the current epoch and then write the epoch into
+  // their flag; I wait for every neighbour's flag and copy the slot into the ghost tail.
+  // Double buffering is enough: a neighbour can only be one epoch ahead of me, because
+  // its next push is stream-ordered after its wait for my previous one.
+  void setup_peer_halo();
+  template <typename T>
+  void exchange_forward_peer(T* vec_data, void* stream) const;
+  bool _peer_ok = false;
+  char* _stage = nullptr;            // my staging buffer (cudaMalloc, IPC-exported)
+  size_t _slot_bytes = 0;
+  std::vector<char*> _peer_stage;    // per neighbour: its staging buffer mapped here
+  std::vector<size_t> _peer_slot_bytes;
+  std::vector<std::int64_t> _land;   // per neighbour: element offset of my slice in its ghost tail
+  mutable std::uint32_t _epoch = 0;
 };
 
 } // namespace spmv

@@ -30,6 +30,12 @@ SIGNATURES = {
     "b200_host_alloc_pinned": [C.POINTER(_p), _sz],
     "b200_host_free_pinned": [_p],
     "b200_stream_create": [C.POINTER(_p)],
+    "b200_stream_create_priority": [C.POINTER(_p), _int],
+    "b200_ipc_alloc": [C.POINTER(_p), _sz, C.c_char_p],
+    "b200_ipc_open": [C.POINTER(_p), C.c_char_p],
+    "b200_ipc_close": [_p],
+    "b200_stream_write_u32": [_p, _p, C.c_uint32],
+    "b200_stream_wait_u32_geq": [_p, _p, C.c_uint32],
     "b200_stream_destroy": [_p],
     "b200_stream_synchronize": [_p],
     "b200_event_create": [C.POINTER(_p), _int],

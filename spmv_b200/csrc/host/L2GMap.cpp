@@ -9,6 +9,8 @@
 #include "host_util.h"
 
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <stdexcept>
 
 using namespace spmv;
@@ -112,8 +114,116 @@ L2GMap::L2GMap(MPI_Comm comm, std::int64_t local_size, const std::vector<std::in
   }
 
   // The NCCL communicator is created once per executor, collectively.
-  if (const B200Executor* gpu = as_b200(_exec))
+  if (const B200Executor* gpu = as_b200(_exec)) {
     gpu->attach_comm(comm);
+    if (mpi_size > 1)
+      setup_peer_halo();
+  }
+}
+//-----------------------------------------------------------------------------
+// Collective.  Every rank exports a staging buffer and tells the others where their
+// slices land in it; neighbours map each other's buffers.  If any rank cannot (ranks
+// sharing a process, IPC or stream memory operations unavailable, B200_HALO=nccl) all
+// ranks keep the NCCL send/recv exchange.
+void L2GMap::setup_peer_halo()
+{
+  const B200Executor* gpu = as_b200(_exec);
+  int mpi_size = 0;
+  CHECK_MPI(MPI_Comm_size(_comm, &mpi_size));
+  const int nnbr = static_cast<int>(_neighbours.size());
+  const std::int64_t local_size = _ranges[_mpi_rank + 1] - _ranges[_mpi_rank];
+  const char* mode = std::getenv("B200_HALO");
+  int ok = !(mode && std::strcmp(mode, "nccl") == 0);
+  detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+
+  struct Card {
+    char handle[B200_IPC_HANDLE_BYTES];
+    std::int64_t slot_bytes;
+    std::int64_t ok;
+  };
+  Card mine;
+  std::memset(&mine, 0, sizeof(mine));
+  _slot_bytes = (sizeof(double) * std::max<size_t>(_ghosts.size(), 1) + 255) / 256 * 256;
+  const size_t total = 2 * _slot_bytes + sizeof(std::uint32_t) * static_cast<size_t>(mpi_size);
+  void* stage = nullptr;
+  if (ok && b200_ipc_alloc(&stage, total, mine.handle) != B200_OK)
+    ok = 0;
+  // stream memory operations present?  (probe: a write to my own flag word)
+  if (ok && b200_stream_write_u32(gpu->comm_stream(), static_cast<char*>(stage) + 2 * _slot_bytes, 0u) != B200_OK)
+    ok = 0;
+  _stage = static_cast<char*>(stage);
+  mine.slot_bytes = static_cast<std::int64_t>(_slot_bytes);
+  mine.ok = ok;
+
+  std::vector<Card> cards(mpi_size);
+  CHECK_MPI(MPI_Allgather(&mine, static_cast<int>(sizeof(Card)), MPI_CHAR, cards.data(), static_cast<int>(sizeof(Card)),
+                          MPI_CHAR, _comm));
+  // land_mine[q]: element offset in my ghost tail where rank q's slice goes (-1: none)
+  std::vector<std::int64_t> land_mine(mpi_size, -1), land_all(static_cast<size_t>(mpi_size) * mpi_size, -1);
+  for (int i = 0; i < nnbr; ++i)
+    land_mine[_neighbours[i]] = _send_offset[i] - local_size;
+  CHECK_MPI(MPI_Allgather(land_mine.data(), mpi_size, MPI_INT64_T, land_all.data(), mpi_size, MPI_INT64_T, _comm));
+  for (const Card& c : cards)
+    ok = ok && c.ok != 0;
+
+  _peer_stage.assign(nnbr, nullptr);
+  _peer_slot_bytes.assign(nnbr, 0);
+  _land.assign(nnbr, -1);
+  if (ok) {
+    for (int i = 0; i < nnbr; ++i) {
+      const int q = _neighbours[i];
+      void* p = nullptr;
+      if (b200_ipc_open(&p, cards[q].handle) != B200_OK) {
+        ok = 0;
+        break;
+      }
+      _peer_stage[i] = static_cast<char*>(p);
+      _peer_slot_bytes[i] = static_cast<size_t>(cards[q].slot_bytes);
+      _land[i] = land_all[static_cast<size_t>(q) * mpi_size + _mpi_rank];
+    }
+  }
+  int all_ok = 0;
+  CHECK_MPI(MPI_Allreduce(&ok, &all_ok, 1, MPI_INT, MPI_MIN, _comm));
+  _peer_ok = all_ok != 0;
+  if (!_peer_ok) {
+    for (char*& p : _peer_stage) {
+      b200_ipc_close(p);
+      p = nullptr;
+    }
+    if (_stage)
+      b200_free(_stage);
+    _stage = nullptr;
+  }
+}
+//-----------------------------------------------------------------------------
+template <typename T>
+void L2GMap::exchange_forward_peer(T* vec_data, void* stream) const
+{
+  int mpi_size = static_cast<int>(_ranges.size()) - 1;
+  (void)mpi_size;
+  const int nnbr = static_cast<int>(_neighbours.size());
+  const std::uint32_t epoch = ++_epoch;
+  const size_t slot = epoch & 1u;
+  const std::int64_t local_size = _ranges[_mpi_rank + 1] - _ranges[_mpi_rank];
+  // push my slices (L2GMap.cpp:586-598 naming: I SEND _recv_count[i] from _recv_offset[i])
+  for (int i = 0; i < nnbr; ++i) {
+    char* peer = _peer_stage[i];
+    if (_recv_count[i] > 0)
+      detail::check(b200_memcpy_d2d_async(peer + slot * _peer_slot_bytes[i] + sizeof(T) * static_cast<size_t>(_land[i]),
+                                          static_cast<const char*>(_send_buf) + sizeof(T) * static_cast<size_t>(_recv_offset[i]),
+                                          sizeof(T) * static_cast<size_t>(_recv_count[i]), stream),
+                    "peer halo copy");
+    detail::check(b200_stream_write_u32(stream, peer + 2 * _peer_slot_bytes[i] + sizeof(std::uint32_t) * _mpi_rank, epoch),
+                  "peer halo flag");
+  }
+  // wait for every neighbour's slice of this epoch, then move the slot into the ghost tail
+  for (int i = 0; i < nnbr; ++i)
+    detail::check(b200_stream_wait_u32_geq(stream, _stage + 2 * _slot_bytes + sizeof(std::uint32_t) * _neighbours[i], epoch),
+                  "peer halo wait");
+  if (!_ghosts.empty())
+    detail::check(b200_memcpy_d2d_async(vec_data + local_size, _stage + slot * _slot_bytes, sizeof(T) * _ghosts.size(),
+                                        stream),
+                  "peer halo unpack");
 }
 //-----------------------------------------------------------------------------
 L2GMap::~L2GMap()
@@ -127,6 +237,10 @@ L2GMap::~L2GMap()
   _exec->free(_indexbuf);
   _exec->free(_send_buf);
   _exec->free(_recv_buf);
+  for (char* p : _peer_stage)
+    b200_ipc_close(p);
+  if (_stage)
+    b200_free(_stage);
 }
 //-----------------------------------------------------------------------------
 template <typename T>
@@ -144,6 +258,11 @@ template <typename T>
 void L2GMap::exchange_forward(T* vec_data, bool overlap) const
 {
   ensure_send_buf<T>();
+  // the previous exchange may still be reading the send buffer on the side stream if the
+  // caller never finalised it
+  if (const B200Executor* g = as_b200(_exec))
+    if (overlap && !_neighbours.empty())
+      detail::check(b200_stream_wait_event(g->get_cuda_stream(), g->arrived_event()), "stream wait");
   // pack: send_buf[k] = vec[indexbuf[k]]  (throws on the host executor: no CPU path)
   _exec->gather_ghosts_run(_num_indices, _indexbuf, vec_data, static_cast<T*>(_send_buf));
 
@@ -160,6 +279,12 @@ void L2GMap::exchange_forward(T* vec_data, bool overlap) const
     detail::check(b200_event_record(gpu->packed_event(), gpu->get_cuda_stream()), "event record");
     detail::check(b200_stream_wait_event(gpu->comm_stream(), gpu->packed_event()), "stream wait");
     stream = gpu->comm_stream();
+  }
+  if (_peer_ok) {
+    exchange_forward_peer(vec_data, stream);
+    if (overlap)
+      detail::check(b200_event_record(gpu->arrived_event(), gpu->comm_stream()), "event record");
+    return;
   }
   // NB the naming (L2GMap.cpp:520-525): _recv_* describe what I SEND in a forward
   // update, _send_* what I RECEIVE (my ghosts), landing straight in the tail of vec_data.

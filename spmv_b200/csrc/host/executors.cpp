@@ -96,7 +96,7 @@ B200Executor::B200Executor(int device_id, std::shared_ptr<DeviceExecutor> host) 
   _dev_info.type = DeviceType::gpu;
   _dev_info.id = device_id;
   detail::check(b200_set_device(device_id), "B200Executor: cannot select the device");
-  detail::check(b200_stream_create(&_comm_stream), "B200Executor: comm stream");
+  detail::check(b200_stream_create_priority(&_comm_stream, 1), "B200Executor: comm stream");
   detail::check(b200_event_create(&_ev_packed, 0), "B200Executor: event");
   detail::check(b200_event_create(&_ev_arrived, 0), "B200Executor: event");
 }

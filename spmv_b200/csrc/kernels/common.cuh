@@ -70,6 +70,8 @@ struct Plan {
   int32_t* d_tile_meta = nullptr; // 2*(num_tiles+1) ints
   int32_t max_row_len = 0;
   int64_t hist[32] = {0};
+  int32_t* d_rowlist = nullptr;    // ids of the non-empty rows, ascending (sparse-row blocks only)
+  int32_t n_rowlist = 0;
   double* d_partials = nullptr;    // dot epilogue: one partial per CTA
   unsigned int* d_counter = nullptr; // last-CTA-done ticket
   int32_t partials_len = 0;

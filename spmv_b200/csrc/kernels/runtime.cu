@@ -152,6 +152,120 @@ int b200_stream_create(void** stream)
   return B200_OK;
 }
 
+int b200_stream_create_priority(void** stream, int high)
+{
+  B200_REQUIRE(stream != nullptr, "stream is NULL");
+  int least = 0, greatest = 0;
+  B200_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+  cudaStream_t s;
+  B200_CUDA(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, high ? greatest : least));
+  *stream = s;
+  return B200_OK;
+}
+
+// ---- CUDA IPC + stream memory operations (direct peer halo) ------------------------------
+int b200_ipc_alloc(void** d_ptr, size_t num_bytes, char handle[B200_IPC_HANDLE_BYTES])
+{
+  B200_REQUIRE(d_ptr != nullptr && handle != nullptr && num_bytes > 0, "bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200_IPC_HANDLE_BYTES, "IPC handle size");
+  *d_ptr = nullptr;
+  void* p = nullptr;
+  B200_CUDA(cudaMalloc(&p, num_bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaMemset(p, 0, num_bytes);
+  if (e == cudaSuccess)
+    e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return cuda_fail(e, "b200_ipc_alloc", __FILE__, __LINE__);
+  }
+  memcpy(handle, &h, sizeof(h));
+  *d_ptr = p;
+  return B200_OK;
+}
+
+int b200_ipc_open(void** d_peer_ptr, const char handle[B200_IPC_HANDLE_BYTES])
+{
+  B200_REQUIRE(d_peer_ptr != nullptr && handle != nullptr, "bad argument");
+  *d_peer_ptr = nullptr;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  cudaError_t e = cudaIpcOpenMemHandle(d_peer_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) {
+    cudaGetLastError(); // not sticky: the caller falls back to NCCL
+    *d_peer_ptr = nullptr;
+    return cuda_fail(e, "cudaIpcOpenMemHandle", __FILE__, __LINE__);
+  }
+  return B200_OK;
+}
+
+int b200_ipc_close(void* d_peer_ptr)
+{
+  if (d_peer_ptr)
+    B200_CUDA(cudaIpcCloseMemHandle(d_peer_ptr));
+  return B200_OK;
+}
+
+namespace
+{
+// Driver entry points fetched through the runtime (the library does not link libcuda).
+using MemOp32 = int (*)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+struct MemOps {
+  MemOp32 write = nullptr, wait = nullptr;
+  bool tried = false;
+};
+MemOps& memops()
+{
+  static MemOps m;
+  if (!m.tried) {
+    m.tried = true;
+    void *w = nullptr, *a = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &w, cudaEnableDefault, &q1) == cudaSuccess
+        && cudaGetDriverEntryPoint("cuStreamWaitValue32", &a, cudaEnableDefault, &q2) == cudaSuccess
+        && q1 == cudaDriverEntryPointSuccess && q2 == cudaDriverEntryPointSuccess) {
+      m.write = reinterpret_cast<MemOp32>(w);
+      m.wait = reinterpret_cast<MemOp32>(a);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return m;
+}
+} // namespace
+
+int b200_stream_write_u32(void* stream, void* d_flag, uint32_t value)
+{
+  B200_REQUIRE(d_flag != nullptr, "flag is NULL");
+  MemOps& m = memops();
+  if (!m.write) {
+    set_error("cuStreamWriteValue32 is not available from this driver");
+    return B200_ECUDA;
+  }
+  const int rc = m.write(as_stream(stream), (unsigned long long)(uintptr_t)d_flag, value, 0u /* default */);
+  if (rc != 0) {
+    set_error("cuStreamWriteValue32 failed with CUresult %d", rc);
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
+int b200_stream_wait_u32_geq(void* stream, void* d_flag, uint32_t value)
+{
+  B200_REQUIRE(d_flag != nullptr, "flag is NULL");
+  MemOps& m = memops();
+  if (!m.wait) {
+    set_error("cuStreamWaitValue32 is not available from this driver");
+    return B200_ECUDA;
+  }
+  const int rc = m.wait(as_stream(stream), (unsigned long long)(uintptr_t)d_flag, value, 0u /* CU_STREAM_WAIT_VALUE_GEQ */);
+  if (rc != 0) {
+    set_error("cuStreamWaitValue32 failed with CUresult %d", rc);
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
 int b200_stream_destroy(void* stream)
 {
   if (stream != nullptr)

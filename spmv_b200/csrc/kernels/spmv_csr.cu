@@ -35,6 +35,9 @@
 //     shared-memory copy of x (the diagonal block's near band).
 #include "common.cuh"
 
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
+
 #include <algorithm>
 #include <cstdlib>
 #include <new>
@@ -576,6 +579,55 @@ __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
     walk_direct<T, SYM, false>(a, r0 + ns, nrows - ns, warp, NT / 32, lane);
 }
 
+// ---------------------------------------------------------------------------
+// Sparse-row blocks: the remote block of a slab-partitioned operator has entries
+// in the few rows that touch a ghost plane (2 planes of 256 for the Poisson slabs)
+// and is empty elsewhere.  With beta == 1 an empty row leaves y untouched, so only
+// the listed (non-empty) rows are visited: no pass over the whole rowptr and y
+// (335 MB of traffic for 1.2 MB of entries).  One thread per listed row in j order
+// (same roundings as csr_kernels.cpp:45-47), or one warp per row when rows are long.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void spmv_rowlist_kernel(int n, const int32_t* __restrict__ rowlist,
+                                    const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colind,
+                                    const T* __restrict__ val, const T* __restrict__ x, T alpha, T beta,
+                                    T* __restrict__ y)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n)
+    return;
+  const int r = __ldg(rowlist + k);
+  const int rs = __ldg(rowptr + r), re = __ldg(rowptr + r + 1);
+  T sum = 0;
+  for (int j = rs; j < re; ++j)
+    sum = add_rn(sum, mul_rn(__ldg(val + j), __ldg(x + __ldg(colind + j))));
+  y[r] = add_rn(mul_rn(alpha, sum), mul_rn(beta, y[r]));
+}
+
+template <typename T>
+__global__ void spmv_rowlist_warp_kernel(int n, const int32_t* __restrict__ rowlist,
+                                         const int32_t* __restrict__ rowptr,
+                                         const int32_t* __restrict__ colind, const T* __restrict__ val,
+                                         const T* __restrict__ x, T alpha, T beta, T* __restrict__ y)
+{
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (k >= n)
+    return;
+  const int r = __ldg(rowlist + k);
+  const int rs = __ldg(rowptr + r), re = __ldg(rowptr + r + 1);
+  T part = 0;
+  for (int j = rs + lane; j < re; j += 32)
+    part = fma(__ldg(val + j), __ldg(x + __ldg(colind + j)), part);
+  part = warp_sum(part);
+  if (lane == 0)
+    y[r] = add_rn(mul_rn(alpha, part), mul_rn(beta, y[r]));
+}
+
+struct RowNonEmpty {
+  const int32_t* rowptr;
+  __host__ __device__ bool operator()(int r) const { return rowptr[r + 1] > rowptr[r]; }
+};
+
 // Diagonal-only symmetric block (nnz == 0, rowptr == NULL): csr_matrix.cpp:85,
 // openmp/csr_kernels.openmp.cpp:222-225.
 template <typename T>
@@ -880,6 +932,18 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   }
   B200_REQUIRE(d_rowptr && d_colind && d_val, "matrix arrays are NULL but nnz > 0");
 
+  if (!SYM && p.d_rowlist != nullptr && beta == T(1) && d_dot == nullptr) {
+    const int n = p.n_rowlist;
+    if (p.max_row_len <= SHORT_ROW)
+      spmv_rowlist_kernel<T><<<(n + 127) / 128, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
+                                                              alpha, beta, d_y);
+    else
+      spmv_rowlist_warp_kernel<T><<<(n + 7) / 8, 256, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
+                                                               alpha, beta, d_y);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
+
   SpmvArgs<T> a;
   a.rowptr = d_rowptr;
   a.colind = d_colind;
@@ -983,6 +1047,30 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   cudaFree(d_max);
   d_hist = nullptr;
   d_max = nullptr;
+  // sparse-row block (more than half the rows empty): list the non-empty rows
+  if (!p->symmetric && nnz > 0 && p->hist[0] * 2 > (int64_t)rows && env_int("B200_SPMV_ROWLIST", 1)) {
+    const int n_list = (int)((int64_t)rows - p->hist[0]);
+    int* d_num = nullptr;
+    void* d_tmp = nullptr;
+    size_t tmp_bytes = 0;
+    cub::CountingInputIterator<int> ids(0);
+    RowNonEmpty pred{d_rowptr};
+    bool ok = cudaMalloc(&p->d_rowlist, sizeof(int32_t) * (size_t)std::max(n_list, 1)) == cudaSuccess
+              && cudaMalloc(&d_num, sizeof(int)) == cudaSuccess
+              && cub::DeviceSelect::If(nullptr, tmp_bytes, ids, p->d_rowlist, d_num, rows, pred, st) == cudaSuccess
+              && cudaMalloc(&d_tmp, std::max<size_t>(tmp_bytes, 1)) == cudaSuccess
+              && cub::DeviceSelect::If(d_tmp, tmp_bytes, ids, p->d_rowlist, d_num, rows, pred, st) == cudaSuccess;
+    int got = -1;
+    ok = ok && cudaMemcpyAsync(&got, d_num, sizeof(int), cudaMemcpyDeviceToHost, st) == cudaSuccess
+         && cudaStreamSynchronize(st) == cudaSuccess && got == n_list;
+    cudaFree(d_num);
+    cudaFree(d_tmp);
+    if (!ok) {
+      set_error("plan_create: listing the non-empty rows failed (%s)", cudaGetErrorString(cudaGetLastError()));
+      return fail(B200_ECUDA);
+    }
+    p->n_rowlist = n_list;
+  }
   // the histogram picks the walk and its launch shape (environment overrides for
   // sweeps), the walk fixes the stage weights, the weights cut the tiles
   const int variant = env_int("B200_SPMV_VARIANT", 0);
@@ -1008,6 +1096,7 @@ int b200_csr_plan_destroy(void* plan)
   if (!p)
     return B200_OK;
   cudaFree(p->d_tile_meta);
+  cudaFree(p->d_rowlist);
   cudaFree(p->d_partials);
   cudaFree(p->d_counter);
   delete p;

@@ -143,6 +143,33 @@ def test_huge_row_and_empty_rows(cuda, tune):
     assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL
 
 
+@pytest.mark.parametrize("long_rows", [False, True])
+@pytest.mark.parametrize("alpha,beta", [(1.0, 1.0), (-0.5, 1.0), (1.0, 0.0), (2.0, 0.5)])
+def test_sparse_row_block(cuda, long_rows, alpha, beta):
+    """Remote-block shape: most rows empty.  beta == 1 takes the non-empty-row list path (empty rows
+    must keep y bit-for-bit); other betas take the regular walk."""
+    rng = np.random.default_rng(11)
+    n, ncols = 20000, 23000
+    lens = np.zeros(n, dtype=np.int64)
+    hit = rng.choice(n, size=1500, replace=False)
+    lens[hit] = rng.integers(1, 10, size=hit.size)
+    if long_rows:
+        lens[hit[:7]] = [33, 64, 500, 40, 100, 35, 2000]
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens, out=rp[1:])
+    col = np.concatenate([np.sort(rng.choice(ncols, size=l, replace=False)) for l in lens if l]).astype(np.int64)
+    val = rng.standard_normal(rp[-1])
+    x, y0 = rng.standard_normal(ncols), rng.standard_normal(n)
+    y, info = run_general(cuda, rp, col, val, x, ncols, alpha, beta, y0.copy())
+    assert info["hist"][0] == n - hit.size
+    want = OK.spmv(rp, col, val, x, alpha, beta, y0)
+    assert rel_l2(y, want) < TOL
+    if beta == 1.0:
+        assert np.array_equal(y[lens == 0], y0[lens == 0])
+        if not long_rows:
+            assert np.array_equal(y, want)  # one thread per row, reference order
+
+
 def test_zero_rows_and_zero_nnz(cuda):
     y, info = run_general(cuda, np.zeros(1, np.int32), np.zeros(0, np.int32), np.zeros(0), np.zeros(4), 4)
     assert y.size == 0 and info["num_tiles"] == 0
