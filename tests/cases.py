@@ -14,6 +14,13 @@ def fixture_rows(r0, r1):
     return rp, FIX_COLIND[sl].astype(np.int64), FIX_VALUES[sl].copy()
 
 
+def problem_name(kind, n=None):
+    """Key of a problem in tests/golden/plans_and_blocks.npz."""
+    if n is None:
+        return kind
+    return kind + "_" + ("x".join(str(v) for v in n) if isinstance(n, tuple) else str(n))
+
+
 def make_problem(kind, n=None):
     """-> (N_global, rows_fn)"""
     if kind == "fixture":

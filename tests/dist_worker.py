@@ -81,7 +81,29 @@ def main():
         if not cond:
             failures.append(what)
 
-    problems = [("fixture", None), ("lap27", (6, 5, 8)), ("lap7", (7, 6, 8)), ("powerlaw", 4000), ("create_a", 1001)]
+    golden_path = os.path.join(ROOT, "tests", "golden", "plans_and_blocks.npz")
+    golden = np.load(golden_path) if os.path.exists(golden_path) else None
+
+    def check_golden(A, name, sym, cm, tag):
+        """Plans and blocks against the committed output of the reference's own code."""
+        key = f"{name}/s{size}/sym{int(sym)}/cm{cm}/r{rank}"
+        if golden is None or f"{key}/non_zeros" not in golden.files:
+            return
+        plan = A.col_map().plan()
+        for k in cases.PLAN_KEYS:
+            check(np.array_equal(np.asarray(plan[k]), golden[f"{key}/plan/{k}"]), tag + f": golden plan {k} differs")
+        for name, blk in (("local", A.local_block()), ("remote", A.remote_block())):
+            have = f"{key}/{name}/dims" in golden.files
+            check((blk is not None) == have, tag + f": golden {name} block presence differs")
+            if blk is None or not have:
+                continue
+            for k in ("rowptr", "colind", "values"):
+                check(np.array_equal(blk[k], golden[f"{key}/{name}/{k}"]), tag + f": golden {name} {k} differs")
+            if blk["diagonal"] is not None:
+                check(np.array_equal(blk["diagonal"], golden[f"{key}/{name}/diagonal"]), tag + ": golden diagonal differs")
+        check(A.non_zeros() == int(golden[f"{key}/non_zeros"]), tag + ": golden non_zeros differs")
+
+    problems = [("fixture", None), ("lap7", (4, 3, 6)), ("lap27", (6, 5, 8)), ("lap7", (7, 6, 8)), ("powerlaw", 4000), ("create_a", 1001)]
     combos = [(False, api.P2P_BLOCKING), (False, api.P2P_NONBLOCKING), (False, api.COLLECTIVE_BLOCKING),
               (False, api.COLLECTIVE_NONBLOCKING), (True, api.COLLECTIVE_BLOCKING), (True, api.P2P_NONBLOCKING)]
     for kind, n in problems:
@@ -97,6 +119,7 @@ def main():
             A = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
                                          inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
             plan = A.col_map().plan()
+            check_golden(A, cases.problem_name(kind, n), sym, cm, tag)
             if ref is not None:
                 check(cases.same_plan(plan, ref["plan"]), tag + ": column map plan differs")
                 check(cases.same_plan(A.row_map().plan(), ref["rowplan"]), tag + ": row map plan differs")

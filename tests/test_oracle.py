@@ -1,5 +1,7 @@
 """CPU: pin the oracle (plain-C restatement) against the reference's golden values
 and, where oracle/_ref was built, against the reference's own compiled kernels."""
+import os
+
 import numpy as np
 import pytest
 import scipy.sparse as sp
@@ -103,3 +105,69 @@ def test_blas1_restatement():
     assert np.array_equal(y2, y + 0.3 * x)
     K.dscal(-1.5, y2)
     assert np.array_equal(y2, (y + 0.3 * x) * -1.5)
+
+
+# ---------------------------------------------------------------------------------------------
+# golden vectors (tests/golden/*.npz, written by tests/golden/make_golden.py from the reference's
+# own compiled code) and the restated CG
+# ---------------------------------------------------------------------------------------------
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CG_GOLDEN = ["lap27_6x5x8", "lap7_12x12x12", "powerlaw_3000"]
+
+
+def test_golden_fixture_matches_restated_kernels():
+    g = np.load(os.path.join(GOLDEN, "fixture_5x5.npz"))
+    assert np.array_equal(g["x"], FIX_X)
+    assert np.array_equal(K.spmv(FIX_ROWPTR, FIX_COLIND, FIX_VALUES, FIX_X), g["y_general"])
+    assert np.array_equal(K.symv(FIX_SYM_ROWPTR, FIX_SYM_COLIND, FIX_SYM_VALUES, FIX_SYM_DIAG, FIX_X), g["y_symmetric"])
+    assert abs(np.linalg.norm(g["y_general"]) - 1.3857542692681533) <= 2.3e-16 * 1.3857542692681533
+
+
+@pytest.mark.parametrize("name", CG_GOLDEN)
+def test_restated_cg_reproduces_golden(name):
+    """The golden iteration count and x are the reference's cg.cpp at 1 rank: the restatement must hit
+    them bit for bit, and then its residual history is the reference's trajectory."""
+    from oracle import cg as OCG
+    g = np.load(os.path.join(GOLDEN, f"cg_{name}.npz"))
+    mult = lambda p: K.spmv(g["rowptr"], g["colind"], g["values"], p)  # noqa: E731
+    it, x, hist = OCG.cg(mult, g["b"], int(g["kmax"]), float(g["rtol"]))
+    assert it == int(g["iterations"])
+    assert np.array_equal(x, g["x"])
+    assert np.array_equal(hist, g["history"])
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,n", [("lap7", (7, 6, 8)), ("lap27", (6, 5, 8)), ("create_a", 1001)])
+def test_restated_cg_equals_reference(kind, n):
+    """Ladder of kmax values through the reference's own cg.cpp (tier 2): same iteration counts, and
+    bit-identical x at 1 rank (the whole trajectory); <= 1e-14 at 2 and 3 thread-ranks, where the
+    reference sums each row in local-column order."""
+    from oracle import cg as OCG
+    from oracle import ref_api as R
+    from tests import cases
+    if not R.available():
+        pytest.skip("oracle/_ref/libspmv_ref.so not built")
+    N, rows = cases.make_problem(kind, n)
+    rp, col, val = rows(0, N)
+    rp32, c32 = rp.astype(np.int32), col.astype(np.int32)
+    mult = lambda p: K.spmv(rp32, c32, val, p)  # noqa: E731
+    b = mult(np.ones(N))
+    for size in (1, 2, 3):
+        for kmax, rtol in ((5, 1e-30), (17, 1e-30), (200, 1e-8)):
+            out = {}
+
+            def body(rank):
+                inp = cases.local_inputs(rows, N, rank, size)
+                A = R.RefMatrix.create_matrix(inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                              inp["ncols_local"], [], inp["col_ghosts"], False, 2)
+                out[rank] = A.cg(b[inp["r0"]:inp["r1"]], kmax, rtol)
+                A.close()
+
+            R.run_ranks(size, body)
+            x_ref = np.concatenate([out[r][1] for r in range(size)])
+            it, x, _ = OCG.cg(mult, b, kmax, rtol, ranks=size)
+            assert it == out[0][0]
+            if size == 1:
+                assert np.array_equal(x, x_ref)
+            else:
+                assert np.linalg.norm(x - x_ref) <= 1e-14 * np.linalg.norm(x_ref)
