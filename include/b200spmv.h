@@ -170,9 +170,12 @@ B200_API int b200_stream_wait_u32_geq(void* stream, void* d_flag, uint32_t value
  *        st[6] rtol        st[7] kmax            st[16..] reduction scratch
  *      Every kernel is a no-op once st[4] != 0, so a fixed-length CUDA graph of
  *      iterations reproduces the reference's early exit (cg.cpp:80-81).
- *      Reductions are deterministic (fixed grid, fixed-order tree). -------- */
+ *      Reductions are deterministic (fixed grid, fixed-order tree) and carried in twice
+ *      the working precision (error-free products and sums, Dot2): a dot product rounds
+ *      to the same double whatever the summation order, which keeps CG trajectories
+ *      reproducible across implementations. -------- */
 #define B200_CG_STATE_DOUBLES 4096
-#define B200_DOT_SCRATCH_DOUBLES 2048
+#define B200_DOT_SCRATCH_DOUBLES 4096
 /* d_out[0] = sum a[i]*b[i].  d_scratch: B200_DOT_SCRATCH_DOUBLES doubles, zeroed
  * once by the caller before first use.  If d_done_flag != NULL and
  * *d_done_flag != 0 the kernel does nothing. */

@@ -2,16 +2,17 @@
 
 Follows spmv/cg.cpp:21-98 statement by statement -- same scalar expressions (alpha from the
 *rooted* norms squared again, cg.cpp:66; beta likewise, :78), same vector updates through the
-restated BLAS-1 of oracle/restated/kernels.c (left-to-right ddot) -- but keeps ||r_k|| of every
+restated BLAS-1 of oracle/restated/kernels.c (ddot in twice the working precision, Dot2) -- but keeps ||r_k|| of every
 iteration, which the reference computes and throws away (cg.cpp:76-77).  `ranks` > 1 restates the
 MPI version: rows are cut with owner_ranges (read_petsc.cpp:20-36), every dot product is summed
-per rank left to right and the partial sums are folded in rank order, which is what the oracle
+per rank and the (rounded) partial sums are folded in rank order, which is what the oracle
 build's MPI shim does for MPI_Allreduce.
 
 Pinned by tests/test_oracle.py::test_restated_cg_equals_reference against the reference's own
 cg.cpp (oracle/_ref, tier 2): identical iteration counts and bit-identical solutions for a ladder
 of kmax values, i.e. the same trajectory.  What stays UNPINNED is the reference's choice of BLAS
-(un-vendored, CMakeLists.txt:71): the summation order of cblas_ddot is ours.
+(un-vendored, CMakeLists.txt:71): the accuracy and summation order of cblas_ddot are ours
+(oracle/shims/cblas.h).
 """
 import numpy as np
 

@@ -88,9 +88,31 @@ void oracle_scatter_add_f64(int32_t n, const int32_t* indices, const double* in,
 }
 
 /* cg.cpp:47,63,73 -- cblas_ddot with unit strides.  The reference's BLAS is an
- * un-vendored, un-pinned system library (CMakeLists.txt:71); its summation
- * order is unknown.  This restatement fixes the order: left to right. */
+ * un-vendored, un-pinned system library (CMakeLists.txt:71); its summation order and
+ * accuracy are unknown, so the dot product is ours to define.  The definition: the
+ * left-to-right sum evaluated in twice the working precision (Ogita, Rump & Oishi's
+ * Dot2: products split exactly with fma, additions with TwoSum, errors carried along),
+ * rounded once at the end.  Such a value does not depend on the summation order except
+ * with probability ~1e-14, so an implementation that sums in another order (the GPU's
+ * tree) follows the same CG trajectory instead of drifting apart by a factor ~2 per
+ * iteration.  oracle_ddot_plain keeps the naive loop for comparison. */
+#include <math.h>
 double oracle_ddot(int32_t n, const double* x, const double* y)
+{
+  double hi = 0.0, lo = 0.0;
+  for (int32_t i = 0; i < n; ++i) {
+    const double p = x[i] * y[i];
+    const double pe = fma(x[i], y[i], -p);
+    const double s = hi + p;
+    const double bb = s - hi;
+    const double e = (hi - (s - bb)) + (p - bb);
+    hi = s;
+    lo = lo + (e + pe);
+  }
+  return hi + lo;
+}
+
+double oracle_ddot_plain(int32_t n, const double* x, const double* y)
 {
   double s = 0.0;
   for (int32_t i = 0; i < n; ++i)

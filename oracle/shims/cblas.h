@@ -1,8 +1,10 @@
 /* oracle/shims/cblas.h -- TEST INFRASTRUCTURE.
- * The three BLAS-1 calls of cg.cpp:47-85, restated as plain left-to-right loops.
- * The reference links an un-vendored, un-pinned system BLAS (CMakeLists.txt:71), so
- * its summation order is not recoverable; this is a documented choice ("parity
- * unpinned" for CG).  Definitions live in oracle/restated/kernels.c. */
+ * The three BLAS-1 calls of cg.cpp:47-85.  The reference links an un-vendored,
+ * un-pinned system BLAS (CMakeLists.txt:71), so its summation order is not recoverable;
+ * ours is a documented choice ("parity unpinned" for CG): daxpy / dscal are
+ * plain loops, ddot is the left-to-right sum in twice the working precision (Dot2), which
+ * makes the value independent of the summation order.  Definitions live in
+ * oracle/restated/kernels.c. */
 #pragma once
 #ifdef __cplusplus
 extern "C" {

@@ -72,7 +72,7 @@ SIGNATURES = {
 }
 
 CG_STATE_DOUBLES = 4096
-DOT_SCRATCH_DOUBLES = 2048
+DOT_SCRATCH_DOUBLES = 4096
 NCCL_UNIQUE_ID_BYTES = 128
 
 

@@ -26,51 +26,24 @@ enum { ST_RNORM_OLD = 0, ST_PAP = 1, ST_RR = 2, ST_RNORM0 = 3, ST_DONE = 4, ST_I
        ST_RTOL = 6, ST_KMAX = 7, ST_COUNTER = 16, ST_PARTIALS = 32 };
 
 constexpr int VEC_THREADS = 256;
+// per-CTA partials: hi parts in [0, DOT_PARTIALS), lo parts in [DOT_PARTIALS, 2*DOT_PARTIALS)
+constexpr int DOT_PARTIALS = 2000;
+static_assert(ST_PARTIALS + 2 * DOT_PARTIALS <= B200_CG_STATE_DOUBLES, "state block too small");
+static_assert(8 + 2 * DOT_PARTIALS <= B200_DOT_SCRATCH_DOUBLES, "dot scratch too small");
 
 static int vec_grid(int n)
 {
   const int want = (n + VEC_THREADS * 4 - 1) / (VEC_THREADS * 4);
-  const int cap = std::min(num_sms() * 8, B200_CG_STATE_DOUBLES - ST_PARTIALS);
+  const int cap = std::min(num_sms() * 8, DOT_PARTIALS);
   return std::max(1, std::min(want, cap));
 }
 
-// Fold one double per thread over the whole grid into out[0] (deterministic).
-__device__ __forceinline__ bool grid_sum(double v, double* partials, unsigned int* counter,
-                                         double* out)
+// Fold one dd value per thread over the whole grid into out[0] (deterministic, and in twice
+// the working precision: see common.cuh).  partials: 2 * plen doubles.
+__device__ __forceinline__ bool grid_sum(dd v, double* partials, int plen, unsigned int* counter, double* out)
 {
-  __shared__ double s_warp[VEC_THREADS / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  v = warp_sum(v);
-  if (lane == 0)
-    s_warp[warp] = v;
-  __syncthreads();
-  bool last = false;
-  if (warp == 0) {
-    unsigned int ticket = 0;
-    if (lane == 0) {
-      double t = 0.0;
-#pragma unroll
-      for (int w = 0; w < VEC_THREADS / 32; ++w)
-        t += s_warp[w];
-      partials[blockIdx.x] = t;
-      __threadfence();
-      ticket = atomicAdd(counter, 1u);
-    }
-    ticket = __shfl_sync(0xffffffffu, ticket, 0);
-    if (ticket == gridDim.x - 1) {
-      __threadfence();
-      double s = 0.0;
-      for (int i = lane; i < (int)gridDim.x; i += 32)
-        s += __ldcg(partials + i);
-      s = warp_sum(s);
-      if (lane == 0) {
-        out[0] = s;
-        *counter = 0u;
-      }
-      last = true;
-    }
-  }
-  return last;
+  __shared__ double s_warp[2 * (VEC_THREADS / 32)];
+  return grid_dd_reduce(v, threadIdx.x, VEC_THREADS, 1, s_warp, partials, plen, counter, out);
 }
 
 __global__ void __launch_bounds__(VEC_THREADS)
@@ -79,7 +52,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
 {
   if (done_flag != nullptr && *done_flag != 0.0)
     return;
-  double acc = 0.0;
+  dd acc = {0.0, 0.0};
   const int stride = gridDim.x * blockDim.x;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int n2 = n >> 1;
@@ -87,12 +60,12 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const double2* b2 = reinterpret_cast<const double2*>(b);
   for (int i = tid; i < n2; i += stride) {
     const double2 u = __ldg(a2 + i), w = __ldg(b2 + i);
-    acc = fma(u.x, w.x, acc);
-    acc = fma(u.y, w.y, acc);
+    dd_add_prod(acc, u.x, w.x);
+    dd_add_prod(acc, u.y, w.y);
   }
   if ((n & 1) && tid == 0)
-    acc = fma(a[n - 1], b[n - 1], acc);
-  grid_sum(acc, scratch + 8, reinterpret_cast<unsigned int*>(scratch), out);
+    dd_add_prod(acc, a[n - 1], b[n - 1]);
+  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out);
 }
 
 // Unaligned fallback (pointer not 16-byte aligned): scalar loads.
@@ -103,11 +76,11 @@ __global__ void __launch_bounds__(VEC_THREADS)
 {
   if (done_flag != nullptr && *done_flag != 0.0)
     return;
-  double acc = 0.0;
+  dd acc = {0.0, 0.0};
   const int stride = gridDim.x * blockDim.x;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    acc = fma(__ldg(a + i), __ldg(b + i), acc);
-  grid_sum(acc, scratch + 8, reinterpret_cast<unsigned int*>(scratch), out);
+    dd_add_prod(acc, __ldg(a + i), __ldg(b + i));
+  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out);
 }
 
 __global__ void init_state_kernel(double* st, const double* rr, double rtol, int kmax)
@@ -133,16 +106,16 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const double rn = st[ST_RNORM_OLD];
   const double alpha = (rn * rn) / st[ST_PAP]; // cg.cpp:66
   const double nalpha = -alpha;
-  double acc = 0.0;
+  dd acc = {0.0, 0.0};
   const int stride = gridDim.x * blockDim.x;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const double pi = p[i], api = Ap[i];
     x[i] = __dadd_rn(x[i], __dmul_rn(alpha, pi));          // cg.cpp:69
     const double ri = __dadd_rn(r[i], __dmul_rn(nalpha, api)); // cg.cpp:70
     r[i] = ri;
-    acc = fma(ri, ri, acc);                                // cg.cpp:73
+    dd_add_prod(acc, ri, ri);                              // cg.cpp:73
   }
-  grid_sum(acc, st + ST_PARTIALS, reinterpret_cast<unsigned int*>(st + ST_COUNTER), st + ST_RR);
+  grid_sum(acc, st + ST_PARTIALS, DOT_PARTIALS, reinterpret_cast<unsigned int*>(st + ST_COUNTER), st + ST_RR);
 }
 
 __global__ void __launch_bounds__(VEC_THREADS)

@@ -146,6 +146,105 @@ __device__ __forceinline__ T warp_sum(T v)
   return v;
 }
 
+// ---------------------------------------------------------------------------
+// Twice-working-precision dot products (Ogita, Rump & Oishi's Dot2): every product is
+// split exactly with an FMA, every addition with TwoSum, the rounding errors are carried
+// in `lo`.  The result hi+lo is what a sum in ~106-bit arithmetic would give, so two
+// evaluations in DIFFERENT orders (GPU tree here, left-to-right loop in the CPU oracle,
+// any grid size) round to the same double except with probability ~1e-14 per dot.
+// That is what keeps a CG residual history reproducible across implementations: a
+// 1e-16 difference in one dot product grows by ~2x per iteration otherwise.  The
+// kernels are bandwidth-bound; the ~10 extra flops per element are free.
+// ---------------------------------------------------------------------------
+struct dd {
+  double hi, lo;
+};
+__device__ __forceinline__ void dd_two_sum(double a, double b, double& s, double& e)
+{
+  s = __dadd_rn(a, b);
+  const double bb = __dadd_rn(s, -a);
+  e = __dadd_rn(__dadd_rn(a, -__dadd_rn(s, -bb)), __dadd_rn(b, -bb));
+}
+__device__ __forceinline__ void dd_add_prod(dd& acc, double a, double b)
+{
+  const double p = __dmul_rn(a, b);
+  const double pe = __fma_rn(a, b, -p);
+  double s, e;
+  dd_two_sum(acc.hi, p, s, e);
+  acc.hi = s;
+  acc.lo = __dadd_rn(acc.lo, __dadd_rn(e, pe));
+}
+__device__ __forceinline__ dd dd_merge(dd a, dd b)
+{
+  double s, e;
+  dd_two_sum(a.hi, b.hi, s, e);
+  dd r;
+  r.hi = s;
+  r.lo = __dadd_rn(__dadd_rn(a.lo, b.lo), e);
+  return r;
+}
+__device__ __forceinline__ dd dd_warp_sum(dd v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    dd w;
+    w.hi = __shfl_xor_sync(0xffffffffu, v.hi, o);
+    w.lo = __shfl_xor_sync(0xffffffffu, v.lo, o);
+    v = dd_merge(v, w);
+  }
+  return v;
+}
+// Grid-wide dd sum of one value per thread of the first `nthreads` threads of every CTA:
+// warp tree -> per-CTA partial (hi at partials[cta], lo at partials[plen + cta]) -> the
+// last CTA folds the partials.  s_warp: 2 * (nthreads/32) doubles of shared memory.
+// Returns true in the threads of the folding warp of the last CTA.
+__device__ __forceinline__ bool grid_dd_reduce(dd v, int tid, int nthreads, int bar_id, double* s_warp,
+                                               double* partials, int plen, unsigned int* counter,
+                                               double* out)
+{
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
+  v = dd_warp_sum(v);
+  if (lane == 0) {
+    s_warp[2 * warp] = v.hi;
+    s_warp[2 * warp + 1] = v.lo;
+  }
+  named_bar_sync(bar_id, nthreads);
+  bool last = false;
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < nwarps ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < nwarps ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    unsigned int ticket = 0;
+    if (lane == 0) {
+      partials[blockIdx.x] = t.hi;
+      partials[plen + blockIdx.x] = t.lo;
+      __threadfence();
+      ticket = atomicAdd(counter, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) {
+      __threadfence();
+      dd s;
+      s.hi = 0.0;
+      s.lo = 0.0;
+      for (int i = lane; i < (int)gridDim.x; i += 32) {
+        dd w;
+        w.hi = __ldcg(partials + i);
+        w.lo = __ldcg(partials + plen + i);
+        s = dd_merge(s, w);
+      }
+      s = dd_warp_sum(s);
+      if (lane == 0) {
+        out[0] = __dadd_rn(s.hi, s.lo);
+        *counter = 0u;
+      }
+      last = true;
+    }
+  }
+  return last;
+}
+
 // Fire-and-forget global add (SASS RED.E.ADD.F64 / .F32).
 // (B200_EXPERIMENT_NO_RED: timing experiments only -- wrong results -- to read the
 // in-situ cost of the scatter off a kernel that otherwise does the same work.)
@@ -153,8 +252,17 @@ __device__ __forceinline__ T warp_sum(T v)
 __device__ __forceinline__ void red_add(double* addr, double v) { if (v == 1.2345e300) *addr = v; }
 __device__ __forceinline__ void red_add(float* addr, float v) { if (v == 1.2345e30f) *addr = v; }
 #else
-__device__ __forceinline__ void red_add(double* addr, double v) { atomicAdd(addr, v); }
-__device__ __forceinline__ void red_add(float* addr, float v) { atomicAdd(addr, v); }
+// Explicit PTX: `atomicAdd` with an unused result is only turned into RED when the compiler
+// feels free to; with a fence elsewhere in the kernel it emitted ATOMG (a round trip per
+// entry: 1.6x slower symmetric SpMV).
+__device__ __forceinline__ void red_add(double* addr, double v)
+{
+  asm volatile("red.relaxed.gpu.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void red_add(float* addr, float v)
+{
+  asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
 #endif
 
 } // namespace b200

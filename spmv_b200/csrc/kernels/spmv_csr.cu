@@ -78,7 +78,8 @@ struct SpmvArgs {
   int32_t num_tiles;
   int32_t stage_bytes;
   int32_t stages;
-  double* partials;
+  double* partials; // dot epilogue: 2 * partials_len doubles (hi parts, then lo parts)
+  int32_t partials_len;
   unsigned int* counter;
   double* dot_out;
 };
@@ -176,7 +177,7 @@ __device__ __forceinline__ T store_row(const SpmvArgs<T>& a, int r, T sum)
 // slices are staged too, and gathers that fall on the tile's own rows read the
 // staged x.
 template <typename T, bool SYM, bool LONG, bool DOT, int CHUNK, int LAY>
-__device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsigned char* stage,
+__device__ __forceinline__ dd walk_staged(const SpmvArgs<T>& a, const unsigned char* stage,
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
 {
@@ -188,7 +189,7 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
   const int* sr = reinterpret_cast<const int*>(stage + L.off_r());
   const T* sd = reinterpret_cast<const T*>(stage + L.off_d()) + (r0 - L.lo_d); // diag[r0 + k]
   const T* sx = reinterpret_cast<const T*>(stage + L.off_x()) + (r0 - L.lo_d); // x[r0 + k]
-  double dot = 0.0;
+  dd dot = {0.0, 0.0};
 
   for (int k = tid; k < nrows; k += nthreads) {
     const int r = r0 + k;
@@ -234,7 +235,7 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
     }
     const T out = store_row<T, SYM>(a, r, sum);
     if (DOT)
-      dot += (double)__ldg(a.x + r) * (double)out;
+      dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
   }
 
   if (LONG) {
@@ -249,7 +250,7 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
       if (lane == 0) {
         const T out = store_row<T, SYM>(a, r, sum);
         if (DOT)
-          dot += (double)__ldg(a.x + r) * (double)out;
+          dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
       }
     }
   }
@@ -266,7 +267,7 @@ __device__ __forceinline__ double walk_staged(const SpmvArgs<T>& a, const unsign
 //     the same sequence of roundings as csr_kernels.cpp:45-47 -- and, symmetric
 //     storage, scatters alpha*val*x[row] into y[col] (csr_kernels.cpp:33-37).
 template <typename T, bool SYM, bool LONG, bool DOT>
-__device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned char* stage,
+__device__ __forceinline__ dd walk_stream(const SpmvArgs<T>& a, unsigned char* stage,
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
 {
@@ -282,7 +283,7 @@ __device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned cha
   const T* sx = reinterpret_cast<const T*>(stage + L.off_x()) + (r0 - L.lo_d);     // x[r0 + k]
   T* sp = EXT ? reinterpret_cast<T*>(stage + L.off_p()) : sv;
   const int n = hi - lo;
-  double dot = 0.0;
+  dd dot = {0.0, 0.0};
 
   for (int j0 = tid; j0 < n; j0 += nthreads * U) {
     int c[U];
@@ -330,7 +331,7 @@ __device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned cha
     }
     const T out = store_row<T, SYM>(a, r, sum);
     if (DOT)
-      dot += (double)__ldg(a.x + r) * (double)out;
+      dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
   }
 
   if (LONG) {
@@ -355,7 +356,7 @@ __device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned cha
           part += sd[k] * xi;
         const T out = store_row<T, SYM>(a, r, part);
         if (DOT)
-          dot += (double)__ldg(a.x + r) * (double)out;
+          dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
       }
     }
   }
@@ -364,10 +365,10 @@ __device__ __forceinline__ double walk_stream(const SpmvArgs<T>& a, unsigned cha
 
 // Walk a tile straight from global memory, one warp per row.
 template <typename T, bool SYM, bool DOT>
-__device__ __forceinline__ double walk_direct(const SpmvArgs<T>& a, int r0, int nrows, int warp,
+__device__ __forceinline__ dd walk_direct(const SpmvArgs<T>& a, int r0, int nrows, int warp,
                                               int nwarps, int lane)
 {
-  double dot = 0.0;
+  dd dot = {0.0, 0.0};
   for (int k = warp; k < nrows; k += nwarps) {
     const int r = r0 + k;
     const int rs = __ldg(a.rowptr + r), re = __ldg(a.rowptr + r + 1);
@@ -377,48 +378,10 @@ __device__ __forceinline__ double walk_direct(const SpmvArgs<T>& a, int r0, int 
     if (lane == 0) {
       const T out = store_row<T, SYM>(a, r, sum);
       if (DOT)
-        dot += (double)__ldg(a.x + r) * (double)out;
+        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
     }
   }
   return dot;
-}
-
-// Deterministic grid-wide sum of one double per thread of the first `nthreads`
-// threads: warp tree -> per-CTA partial -> last CTA folds the partials in a
-// fixed order.
-__device__ __forceinline__ void grid_dot_reduce(double v, int tid, int nthreads, int bar_id,
-                                                double* s_warp, double* partials,
-                                                unsigned int* counter, double* out)
-{
-  const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
-  v = warp_sum(v);
-  if (lane == 0)
-    s_warp[warp] = v;
-  named_bar_sync(bar_id, nthreads);
-  if (warp == 0) {
-    double t = 0.0;
-    if (lane == 0) {
-      for (int w = 0; w < nwarps; ++w)
-        t += s_warp[w];
-      partials[blockIdx.x] = t;
-      __threadfence();
-    }
-    unsigned int ticket = 0;
-    if (lane == 0)
-      ticket = atomicAdd(counter, 1u);
-    ticket = __shfl_sync(0xffffffffu, ticket, 0);
-    if (ticket == gridDim.x - 1) {
-      __threadfence();
-      double s = 0.0;
-      for (int i = lane; i < (int)gridDim.x; i += 32)
-        s += __ldcg(partials + i);
-      s = warp_sum(s);
-      if (lane == 0) {
-        out[0] = s;
-        *counter = 0u;
-      }
-    }
-  }
 }
 
 // ---------------------------------------------------------------------------
@@ -504,7 +467,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
     return;
   }
 
-  double dot = 0.0;
+  dd dot = {0.0, 0.0};
   for (int it = 0; it < my_tiles; ++it) {
     const int s = it % stages, use = it / stages;
     mbar_wait(full + s, use & 1);
@@ -512,22 +475,22 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
     const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
     if (ns > 0) {
       if (WALK == WALK_STREAM) {
-        dot += walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32, warp,
-                                              CW, lane, 1);
+        dot = dd_merge(dot, walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32,
+                                                           warp, CW, lane, 1));
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
       } else {
-        dot += walk_staged<T, SYM, LONG, DOT, CHUNK, LAY>(a, smem + (size_t)s * sb, m, threadIdx.x,
-                                                          CW * 32, warp, CW, lane, 1);
+        dot = dd_merge(dot, walk_staged<T, SYM, LONG, DOT, CHUNK, LAY>(a, smem + (size_t)s * sb, m, threadIdx.x,
+                                                                       CW * 32, warp, CW, lane, 1));
       }
     }
     if (ns < nrows)
-      dot += walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane);
+      dot = dd_merge(dot, walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane));
     __syncwarp();
     if (lane == 0)
       mbar_arrive(empty + s);
   }
   if (DOT)
-    grid_dot_reduce(dot, threadIdx.x, CW * 32, 2, s_warp, a.partials, a.counter, a.dot_out);
+    grid_dd_reduce(dot, threadIdx.x, CW * 32, 2, s_warp, a.partials, a.partials_len, a.counter, a.dot_out);
 }
 
 // ---------------------------------------------------------------------------
@@ -958,6 +921,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.stage_bytes = p.stage_bytes;
   a.stages = p.stages;
   a.partials = p.d_partials;
+  a.partials_len = p.partials_len;
   a.counter = p.d_counter;
   a.dot_out = d_dot;
 
@@ -1018,7 +982,7 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
     b200_csr_plan_destroy(p);
     return code;
   };
-  if (cudaMalloc(&p->d_partials, sizeof(double) * p->partials_len) != cudaSuccess
+  if (cudaMalloc(&p->d_partials, sizeof(double) * 2 * p->partials_len) != cudaSuccess
       || cudaMalloc(&p->d_counter, sizeof(unsigned int)) != cudaSuccess
       || cudaMalloc(&d_hist, sizeof(unsigned long long) * 32) != cudaSuccess
       || cudaMalloc(&d_max, sizeof(int)) != cudaSuccess) {

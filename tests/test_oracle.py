@@ -96,10 +96,18 @@ def test_scipy_cross_check():
 def test_blas1_restatement():
     rng = np.random.default_rng(2)
     x, y = rng.standard_normal(1000), rng.standard_normal(1000)
+    # ddot is the sum in twice the working precision (Dot2): it must equal the exactly
+    # rounded dot product (fractions), whatever the order, and stay within an ulp-scale
+    # distance of the naive loop
+    from fractions import Fraction
+    exact = float(sum(Fraction(a) * Fraction(b) for a, b in zip(x.tolist(), y.tolist())))
+    assert K.ddot(x, y) == exact
+    perm = rng.permutation(1000)
+    assert K.ddot(x[perm], y[perm]) == exact
     s = 0.0
     for a, b in zip(x, y):
         s += a * b
-    assert K.ddot(x, y) == s
+    assert abs(K.ddot(x, y) - s) <= 1e-13 * np.abs(x * y).sum()
     y2 = y.copy()
     K.daxpy(0.3, x, y2)
     assert np.array_equal(y2, y + 0.3 * x)
