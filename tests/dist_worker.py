@@ -153,6 +153,12 @@ def main():
                     xr = ref["cg_x"]
                     err = np.linalg.norm(xs.cpu().numpy() - xr) / max(np.linalg.norm(xr), 1e-300)
                     check(err < 1e-7, tag + f": cg x rel err {err}")
+                    if not sym and kind in ("lap27", "lap7") and size <= 2:
+                        # bit-identical SpMV + order-independent (Dot2) dot products on both sides:
+                        # the GPU follows the reference's trajectory exactly (two partial sums add
+                        # commutatively, so this holds at 2 ranks as well)
+                        check(it == ref["cg_it"] and np.array_equal(xs.cpu().numpy(), xr),
+                              tag + f": cg not bit-identical to the reference (its {it} vs {ref['cg_it']}, err {err})")
             A.close()
 
     # device-side builder (demos/CreateLaplace3D.h) against create_matrix on host-generated rows
