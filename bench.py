@@ -345,7 +345,7 @@ def run_b200(args):
         "gpu_launches": head_launches, "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",
                      "frac": head["frac_of_hbm_peak"], "traffic": TRAFFIC_NCU.get("sym7"),
-                     "kernel": "spmv_pipe_kernel<double, SYM, ROW4> (local block; the event pair also spans the "
+                     "kernel": "spmv_pipe_kernel<double, SYM, ROW4S> (local block; the event pair also spans the "
                                "zero-fill of y that precedes it)",
                      "kernel_ms_avg": head["kernel_ms_avg"], "kernel_ms_min": head["kernel_ms_min"],
                      "algorithmic_bytes": bytes_symmetric(cfg["stored_nnz_per_gpu"] if size == 1 else 0, 0,
@@ -360,7 +360,7 @@ def run_b200(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
 # (profiles/): filled in when a capture of the current kernel exists, else null.
-TRAFFIC_NCU = {"sym7": None}
+TRAFFIC_NCU = {"sym7": 1071703000 + 124964608}  # profiles/r01_sym7_row4_ncu_summary.txt
 
 
 # ----------------------------------------------------------------------------

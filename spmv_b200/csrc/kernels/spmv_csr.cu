@@ -49,6 +49,8 @@ namespace b200
 // Walks (template parameter WALK): one thread per row fetching 16 / 8 / 4 entries
 // at a time, or the two-phase stream walk.
 constexpr int WALK_ROW16 = 0, WALK_STREAM = 1, WALK_ROW8 = 2, WALK_ROW4 = 3;
+// ...S: no row is longer than one chunk, so the chunk loop is gone
+constexpr int WALK_ROW8S = 4, WALK_ROW4S = 5;
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
 constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
 constexpr int MAX_STAGE_BYTES = 96 * 1024;
@@ -176,7 +178,7 @@ __device__ __forceinline__ T store_row(const SpmvArgs<T>& a, int r, T sum)
 // for short ones: fewer predicated-off slots).  LAY_DX: the tile's diagonal and x
 // slices are staged too, and gathers that fall on the tile's own rows read the
 // staged x.
-template <typename T, bool SYM, bool LONG, bool DOT, int CHUNK, int LAY>
+template <typename T, bool SYM, bool LONG, bool DOT, int CHUNK, int LAY, bool SINGLE = false>
 __device__ __forceinline__ dd walk_staged(const SpmvArgs<T>& a, const unsigned char* stage,
                                               StageMeta* m, int tid, int nthreads, int warp,
                                               int nwarps, int lane, int bar_id)
@@ -209,6 +211,8 @@ __device__ __forceinline__ dd walk_staged(const SpmvArgs<T>& a, const unsigned c
     // chunk are issued before the first add, so one row keeps up to CHUNK
     // independent L2-latency gathers in flight; the adds then run in j order.
     for (int base = rs; base < re; base += CHUNK) {
+      if (SINGLE && base != rs)
+        break; // (never taken: the plan saw no row longer than CHUNK; lets the compiler drop the loop)
       int c[CHUNK];
       T v[CHUNK], xv[CHUNK];
 #pragma unroll
@@ -398,7 +402,8 @@ template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
   constexpr int LAY = SYM ? (WALK == WALK_STREAM ? LAY_DXP : LAY_DX) : LAY_PLAIN;
-  constexpr int CHUNK = WALK == WALK_ROW4 ? 4 : (WALK == WALK_ROW8 ? 8 : 16);
+  constexpr int CHUNK = (WALK == WALK_ROW4 || WALK == WALK_ROW4S) ? 4 : ((WALK == WALK_ROW8 || WALK == WALK_ROW8S) ? 8 : 16);
+  constexpr bool SINGLE = WALK == WALK_ROW4S || WALK == WALK_ROW8S;
   extern __shared__ __align__(128) unsigned char smem[];
   const int stages = a.stages;
   const int sb = a.stage_bytes;
@@ -479,8 +484,8 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
                                                            warp, CW, lane, 1));
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
       } else {
-        dot = dd_merge(dot, walk_staged<T, SYM, LONG, DOT, CHUNK, LAY>(a, smem + (size_t)s * sb, m, threadIdx.x,
-                                                                       CW * 32, warp, CW, lane, 1));
+        dot = dd_merge(dot, walk_staged<T, SYM, LONG, DOT, CHUNK, LAY, SINGLE>(a, smem + (size_t)s * sb, m,
+                                                                               threadIdx.x, CW * 32, warp, CW, lane, 1));
       }
     }
     if (ns < nrows)
@@ -760,7 +765,7 @@ static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, i
     variant = 0;
   B200_REQUIRE(tile_bytes >= 1024 && tile_bytes + 2048 <= MAX_STAGE_BYTES, "tile_bytes out of range");
   B200_REQUIRE(stages >= 2 && stages <= 8, "stages out of range");
-  B200_REQUIRE(cw == 4 || cw == 8 || cw == 16, "consumer_warps must be 4, 8 or 16");
+  B200_REQUIRE(cw == 8 || cw == 16, "consumer_warps must be 8 or 16");
   B200_REQUIRE(ctas >= 1 && ctas <= 8, "ctas_per_sm out of range");
   p->variant = variant;
   p->tile_bytes = tile_bytes;
@@ -810,8 +815,6 @@ template <typename T, bool SYM, bool DOT, bool LONG, int WALK>
 static int launch_pipe_cw(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
   switch (p.consumer_warps) {
-  case 4:
-    return launch_pipe<T, SYM, DOT, LONG, 4, WALK>(p, a, st);
   case 16:
     return launch_pipe<T, SYM, DOT, LONG, 16, WALK>(p, a, st);
   default:
@@ -826,8 +829,12 @@ static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st
   case WALK_STREAM:
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
   case WALK_ROW8:
+    if (p.max_row_len <= 8)
+      return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW8S>(p, a, st);
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW8>(p, a, st);
   case WALK_ROW4:
+    if (p.max_row_len <= 4)
+      return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW4S>(p, a, st);
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW4>(p, a, st);
   default:
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_ROW16>(p, a, st);

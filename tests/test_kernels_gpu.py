@@ -17,14 +17,14 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-12
 
 VARIANTS = [
-    dict(variant=0, tile_bytes=32768, stages=3, consumer_warps=4, ctas_per_sm=2),
+    dict(variant=0, tile_bytes=32768, stages=3, consumer_warps=8, ctas_per_sm=2),
     dict(variant=0, tile_bytes=4096, stages=2, consumer_warps=16, ctas_per_sm=4),
     dict(variant=0, tile_bytes=65536, stages=3, consumer_warps=8, ctas_per_sm=1),
-    dict(variant=1, tile_bytes=16384, stages=2, consumer_warps=4, ctas_per_sm=2),
+    dict(variant=1, tile_bytes=16384, stages=2, consumer_warps=8, ctas_per_sm=2),
     # forced walks: 2 row/16, 3 stream, 4 row/8, 5 row/4 (b200_csr_plan_tune)
     dict(variant=2, tile_bytes=8192, stages=2, consumer_warps=8, ctas_per_sm=2),
     dict(variant=3, tile_bytes=8192, stages=2, consumer_warps=8, ctas_per_sm=2),
-    dict(variant=3, tile_bytes=2048, stages=3, consumer_warps=4, ctas_per_sm=2),
+    dict(variant=3, tile_bytes=2048, stages=3, consumer_warps=8, ctas_per_sm=2),
     dict(variant=4, tile_bytes=16384, stages=2, consumer_warps=8, ctas_per_sm=3),
     dict(variant=5, tile_bytes=24576, stages=2, consumer_warps=16, ctas_per_sm=2),
 ]
