@@ -217,8 +217,9 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
            "kernel_GBps": op.local_kernel_bytes() / (kern_avg * 1e-3) / 1e9}
     out["frac_of_hbm_peak"] = out["kernel_GBps"] / peak
     if with_e2e:
-        # host buffers: H2D of x and D2H of y inside the timed region, through the executor's
-        # copy_from / copy_to (DeviceExecutor::copy_from, device_executor.h:60-66)
+        # host buffers: H2D of x and D2H of y inside the timed region.  Matrix::mult_host is
+        # copy_from + update + mult + copy_to (demos/spmv_cuda.cpp:71-110) in one call, with the
+        # copies pipelined against the tile ranges when the rank has no neighbours
         M = op.rows
         xh = torch.empty(M, dtype=torch.float64).pin_memory()
         xh.copy_(op.x[:M].cpu())
@@ -226,14 +227,16 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
         xh_np, yh_np = xh.numpy(), yh.numpy()
 
         def e2e_step(_i):
-            op.ex.copy_from_host(op.x, xh_np)
-            op.step()
-            op.ex.copy_to_host(yh_np, op.y)
+            op.A.mult_host(xh_np, yh_np)
 
         n = max(3, min(steps, 10))
         for i in range(3):
             e2e_step(i)
         ms_e2e = timer.run(e2e_step, n) / n
+        op.step()
+        err = float((torch.from_numpy(yh_np) - op.y.cpu()).abs().max() / op.y.abs().max().cpu())
+        if not err <= 1e-13:
+            raise RuntimeError(f"mult_host disagrees with update+mult: rel max err {err}")
         out["e2e"] = {"value": op.algorithmic_bytes() * op.size / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s",
                       "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M}
     return out

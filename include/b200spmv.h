@@ -119,6 +119,24 @@ B200_API int b200_csr_symv_f32(void* plan, const int32_t* d_rowptr, const int32_
                       const float* d_val, const float* d_diag, float alpha,
                       const float* d_x, float beta, float* d_y, void* stream);
 
+/* ---- tile sub-ranges: the plan's tiles are consecutive row ranges of equal stream bytes, so a
+ *      prefix of the rows can be multiplied while the rest of x is still on its way from the
+ *      host (Matrix::mult_host pipelines H2D of x, these launches and D2H of y).
+ *      b200_csr_plan_chunking cuts the tiles into nchunks equal groups and reports, per chunk k,
+ *      tile_bounds[k..k+1], row_bounds[k..k+1] and the smallest / largest column its entries
+ *      touch (col_min INT32_MAX / col_max -1 for an empty chunk).  Host arrays; synchronises.
+ *      The *_tiles_* calls process only the rows of tiles [tile_begin, tile_end).  The
+ *      symmetric one ADDS into y (rows of the range and the columns they scatter to): the
+ *      caller zeroes / scales y once before the first range. ---- */
+B200_API int b200_csr_plan_chunking(void* plan, const int32_t* d_colind, int32_t nchunks, int32_t* tile_bounds,
+                           int32_t* row_bounds, int32_t* col_min, int32_t* col_max, void* stream);
+B200_API int b200_csr_spmv_tiles_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                            const double* d_val, double alpha, const double* d_x, double beta, double* d_y,
+                            int32_t tile_begin, int32_t tile_end, void* stream);
+B200_API int b200_csr_symv_tiles_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                            const double* d_val, const double* d_diag, double alpha, const double* d_x,
+                            double* d_y, int32_t tile_begin, int32_t tile_end, void* stream);
+
 /* ---- halo pack / unpack: DeviceExecutor::gather_ghosts_run
  *      (device_executor.h:123-126; cuda/cuda_executor.cu:9-51) and the
  *      accumulate loop of L2GMap::reverse_update (L2GMap.cpp:920-921). ----- */

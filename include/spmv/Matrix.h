@@ -78,6 +78,12 @@ public:
 
   /// y = A x; x has local_size()+num_ghosts() entries with ghosts updated.
   void mult(T* __restrict__ x, T* __restrict__ y) const;
+  /// y_host = A x_host with both vectors in HOST memory (x_host: local_size() owned entries;
+  /// pinned memory lets the copies overlap).  What the reference's user writes as
+  /// copy_from + update + mult + copy_to (demos/spmv_cuda.cpp:71-110), pipelined: pieces of
+  /// x go up, tile ranges run as their columns land, finished pieces of y come down, all
+  /// at once (mult_host.cpp).  Blocks until y_host is complete.
+  void mult_host(const T* x_host, T* y_host) const;
   /// A^T x: declared by the reference and unimplemented there (Matrix.cpp:143-148);
   /// throws std::runtime_error here too.
   void transpmult(const T* x, T* y) const;
@@ -118,6 +124,7 @@ private:
   std::shared_ptr<spmv::L2GMap> _row_map;
   int _nnz = 0;
   bool _symmetric = false;
+  mutable std::shared_ptr<void> _host_pipe; // device vectors, streams and chunk table of mult_host
 };
 
 } // namespace spmv

@@ -76,6 +76,8 @@ SPMVH_API int spmvh_matrix_block_dims(void* mat, int which, int64_t dims[4]);
 SPMVH_API int spmvh_matrix_block_copy(void* mat, int which, int32_t* rowptr, int32_t* colind, double* values,
                                       double* diagonal);
 SPMVH_API int spmvh_matrix_mult_f64(void* mat, double* d_x, double* d_y); /* Matrix::mult */
+/* Matrix::mult_host: both vectors in host memory (pinned for overlap), copies pipelined with the kernel. */
+SPMVH_API int spmvh_matrix_mult_host_f64(void* mat, const double* x_host, double* y_host);
 /* b200_csr_plan_tune on one block's plan */
 SPMVH_API int spmvh_matrix_tune(void* mat, int which, int variant, int tile_bytes, int stages, int consumer_warps,
                                 int ctas_per_sm);

@@ -48,6 +48,9 @@ SIGNATURES = {
     "b200_csr_plan_destroy": [_p],
     "b200_csr_plan_info": [_p, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i64)],
     "b200_csr_plan_tune": [_p, _p, _int, _int, _int, _int, _int, _p],
+    "b200_csr_plan_chunking": [_p, _p, _i32, _p, _p, _p, _p, _p],
+    "b200_csr_spmv_tiles_f64": [_p, _p, _p, _p, _f64, _p, _f64, _p, _i32, _i32, _p],
+    "b200_csr_symv_tiles_f64": [_p, _p, _p, _p, _p, _f64, _p, _p, _i32, _i32, _p],
     "b200_csr_spmv_f64": [_p, _p, _p, _p, _f64, _p, _f64, _p, _p],
     "b200_csr_spmv_f32": [_p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_csr_spmv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p],

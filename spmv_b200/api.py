@@ -58,6 +58,7 @@ _SIG = {
     "spmvh_matrix_block_dims": [_p, _int, C.POINTER(_i64)],
     "spmvh_matrix_block_copy": [_p, _int, _p, _p, _p, _p],
     "spmvh_matrix_mult_f64": [_p, _p, _p],
+    "spmvh_matrix_mult_host_f64": [_p, _p, _p],
     "spmvh_matrix_tune": [_p, _int, _int, _int, _int, _int, _int],
     "spmvh_cg": [_p, _p, _p, _p, _int, _f64, _p, _int, C.POINTER(_int)],
     "spmvh_write_petsc_matrix": [C.c_char_p, _i32, _i32, _p, _p, _p],
@@ -435,6 +436,12 @@ class Matrix:
 
     def mult(self, x, y):
         _ck(host_lib().spmvh_matrix_mult_f64(self.h, _dev_ptr(x), _dev_ptr(y)))
+
+    def mult_host(self, x_host, y_host):
+        """Matrix::mult_host: numpy (ideally pinned) vectors in, copies pipelined with the kernel."""
+        assert x_host.dtype == np.float64 and y_host.dtype == np.float64
+        assert x_host.flags.c_contiguous and y_host.flags.c_contiguous
+        _ck(host_lib().spmvh_matrix_mult_host_f64(self.h, _np_ptr(x_host), _np_ptr(y_host)))
 
     def tune(self, which=0, variant=0, tile_bytes=49152, stages=2, consumer_warps=8, ctas_per_sm=2):
         _ck(host_lib().spmvh_matrix_tune(self.h, which, variant, tile_bytes, stages, consumer_warps, ctas_per_sm))

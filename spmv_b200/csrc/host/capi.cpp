@@ -290,6 +290,10 @@ int spmvh_matrix_mult_f64(void* mat, double* d_x, double* d_y)
 {
   return guarded([&] { as_mat(mat).mult(d_x, d_y); });
 }
+int spmvh_matrix_mult_host_f64(void* mat, const double* x_host, double* y_host)
+{
+  return guarded([&] { as_mat(mat).mult_host(x_host, y_host); });
+}
 int spmvh_matrix_tune(void* mat, int which, int variant, int tile_bytes, int stages, int consumer_warps,
                       int ctas_per_sm)
 {

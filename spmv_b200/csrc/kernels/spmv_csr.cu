@@ -40,6 +40,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <vector>
 #include <new>
 #include <type_traits>
 
@@ -77,7 +78,8 @@ struct SpmvArgs {
   T alpha;
   T beta;
   const int32_t* tile_meta;
-  int32_t num_tiles;
+  int32_t tile0;     // first tile of this launch (tile sub-ranges: pipelined host-vector SpMV)
+  int32_t num_tiles; // end of the tile range
   int32_t stage_bytes;
   int32_t stages;
   double* partials; // dot epilogue: 2 * partials_len doubles (hi parts, then lo parts)
@@ -422,10 +424,8 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
   }
   __syncthreads();
 
-  const int my_tiles
-      = ((int)blockIdx.x < a.num_tiles)
-            ? (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x
-            : 0;
+  const int span = a.num_tiles - a.tile0;
+  const int my_tiles = ((int)blockIdx.x < span) ? (span - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
   if (warp == CW) {
     if (lane == 0) {
@@ -433,7 +433,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
         const int s = it % stages, use = it / stages;
         if (use > 0)
           mbar_wait(empty + s, (use - 1) & 1);
-        const int tile = blockIdx.x + it * gridDim.x;
+        const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
         const int2 t0 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile);
         const int2 t1 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile + 1);
         const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x;
@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(NT) spmv_tile_kernel(const SpmvArgs<T> a)
   extern __shared__ __align__(128) unsigned char smem[];
   const int sb = a.stage_bytes;
   StageMeta* m = reinterpret_cast<StageMeta*>(smem + sb);
-  const int tile = blockIdx.x;
+  const int tile = a.tile0 + blockIdx.x;
   const int r0 = __ldg(a.tile_meta + 2 * tile), lo = __ldg(a.tile_meta + 2 * tile + 1);
   const int r1 = __ldg(a.tile_meta + 2 * tile + 2);
   const int nrows = r1 - r0;
@@ -673,6 +673,29 @@ __global__ void plan_hist_kernel(const int32_t* __restrict__ rowptr, int rows,
     atomicMax(max_len, s_max);
 }
 
+// Column extent of the entries of each chunk of tiles (b200_csr_plan_chunking).
+__global__ void chunk_extent_kernel(const int32_t* __restrict__ colind, const int32_t* __restrict__ ent_bounds,
+                                    int32_t* __restrict__ cmin, int32_t* __restrict__ cmax)
+{
+  const int k = blockIdx.y;
+  const long long lo = ent_bounds[k], hi = ent_bounds[k + 1];
+  int mn = 0x7fffffff, mx = -1;
+  for (long long j = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; j < hi; j += (long long)gridDim.x * blockDim.x) {
+    const int c = colind[j];
+    mn = min(mn, c);
+    mx = max(mx, c);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0 && mx >= 0) {
+    atomicMin(cmin + k, mn);
+    atomicMax(cmax + k, mx);
+  }
+}
+
 static int env_int(const char* name, int dflt)
 {
   const char* v = std::getenv(name);
@@ -805,7 +828,7 @@ static int launch_pipe(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
   static SmemCache cache;
   if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK>, smem, cache))
     return rc;
-  const int grid = std::min<long long>(p.num_tiles, (long long)num_sms() * p.ctas_per_sm);
+  const int grid = std::min<long long>(a.num_tiles - a.tile0, (long long)num_sms() * p.ctas_per_sm);
   spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK><<<grid, (CW + 1) * 32, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -849,7 +872,7 @@ static int launch_tile(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
   static SmemCache cache;
   if (int rc = set_smem(spmv_tile_kernel<T, SYM, LONG, NT>, smem, cache))
     return rc;
-  spmv_tile_kernel<T, SYM, LONG, NT><<<p.num_tiles, NT, smem, st>>>(a);
+  spmv_tile_kernel<T, SYM, LONG, NT><<<a.num_tiles - a.tile0, NT, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -859,7 +882,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 template <typename T, bool SYM>
 static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_colind, const T* d_val,
                     const T* d_diag, T alpha, const T* d_x, T beta, T* d_y, double* d_dot,
-                    void* stream)
+                    void* stream, int tile_begin = 0, int tile_end = -1)
 {
   B200_REQUIRE(plan_v != nullptr, "plan is NULL");
   const Plan& p = *static_cast<const Plan*>(plan_v);
@@ -873,8 +896,19 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   if (p.rows == 0)
     return B200_OK;
   const int tb = 256, gb = (p.rows + tb - 1) / tb;
+  // tile sub-range (b200_csr_*_tiles_f64): only the rows of tiles [tile_begin, tile_end);
+  // symmetric storage then expects y already prepared (beta*y) by the caller
+  const bool ranged = tile_end >= 0;
+  if (ranged) {
+    B200_REQUIRE(tile_begin >= 0 && tile_begin <= tile_end && tile_end <= p.num_tiles, "bad tile range");
+    B200_REQUIRE(d_dot == nullptr, "tile ranges have no dot epilogue");
+    if (tile_begin == tile_end)
+      return B200_OK;
+  }
 
-  if (SYM) {
+  if (SYM && ranged) {
+    B200_REQUIRE(d_diag != nullptr, "symmetric SpMV needs the diagonal");
+  } else if (SYM) {
     B200_REQUIRE(d_diag != nullptr, "symmetric SpMV needs the diagonal");
     if (p.num_tiles == 0) {
       diag_only_kernel<T><<<gb, tb, 0, st>>>(p.rows, d_diag, d_x, alpha, beta, d_y);
@@ -902,7 +936,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   }
   B200_REQUIRE(d_rowptr && d_colind && d_val, "matrix arrays are NULL but nnz > 0");
 
-  if (!SYM && p.d_rowlist != nullptr && beta == T(1) && d_dot == nullptr) {
+  if (!SYM && !ranged && p.d_rowlist != nullptr && beta == T(1) && d_dot == nullptr) {
     const int n = p.n_rowlist;
     if (p.max_row_len <= SHORT_ROW)
       spmv_rowlist_kernel<T><<<(n + 127) / 128, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
@@ -924,7 +958,8 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.alpha = alpha;
   a.beta = beta;
   a.tile_meta = p.d_tile_meta;
-  a.num_tiles = p.num_tiles;
+  a.tile0 = ranged ? tile_begin : 0;
+  a.num_tiles = ranged ? tile_end : p.num_tiles;
   a.stage_bytes = p.stage_bytes;
   a.stages = p.stages;
   a.partials = p.d_partials;
@@ -1102,6 +1137,71 @@ int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int til
     return rc;
   B200_CUDA(cudaStreamSynchronize(as_stream(stream)));
   return B200_OK;
+}
+
+int b200_csr_plan_chunking(void* plan, const int32_t* d_colind, int32_t nchunks, int32_t* tile_bounds,
+                           int32_t* row_bounds, int32_t* col_min, int32_t* col_max, void* stream)
+{
+  B200_REQUIRE(plan != nullptr && nchunks >= 1 && tile_bounds && row_bounds && col_min && col_max, "bad argument");
+  const Plan* p = static_cast<const Plan*>(plan);
+  cudaStream_t st = as_stream(stream);
+  std::vector<int32_t> meta(2 * ((size_t)p->num_tiles + 1), 0), ent(nchunks + 1, 0);
+  if (p->num_tiles > 0)
+    B200_CUDA(cudaMemcpyAsync(meta.data(), p->d_tile_meta, sizeof(int32_t) * meta.size(), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  for (int k = 0; k <= nchunks; ++k) {
+    const long long t = (long long)p->num_tiles * k / nchunks;
+    tile_bounds[k] = (int32_t)t;
+    row_bounds[k] = p->num_tiles > 0 ? meta[2 * t] : (k == nchunks ? p->rows : 0);
+    ent[k] = p->num_tiles > 0 ? meta[2 * t + 1] : 0;
+  }
+  row_bounds[nchunks] = p->rows;
+  for (int k = 0; k < nchunks; ++k) {
+    col_min[k] = 0x7fffffff;
+    col_max[k] = -1;
+  }
+  if (p->num_tiles == 0 || d_colind == nullptr)
+    return B200_OK;
+  int32_t *d_ent = nullptr, *d_mm = nullptr;
+  B200_CUDA(cudaMalloc(&d_ent, sizeof(int32_t) * (nchunks + 1)));
+  if (cudaMalloc(&d_mm, sizeof(int32_t) * 2 * nchunks) != cudaSuccess) {
+    cudaFree(d_ent);
+    set_error("cudaMalloc failed in plan_chunking");
+    return B200_ENOMEM;
+  }
+  std::vector<int32_t> mm(2 * (size_t)nchunks);
+  std::copy(col_min, col_min + nchunks, mm.begin());
+  std::copy(col_max, col_max + nchunks, mm.begin() + nchunks);
+  cudaMemcpyAsync(d_ent, ent.data(), sizeof(int32_t) * (nchunks + 1), cudaMemcpyHostToDevice, st);
+  cudaMemcpyAsync(d_mm, mm.data(), sizeof(int32_t) * 2 * nchunks, cudaMemcpyHostToDevice, st);
+  chunk_extent_kernel<<<dim3(num_sms() * 2, nchunks), 256, 0, st>>>(d_colind, d_ent, d_mm, d_mm + nchunks);
+  cudaMemcpyAsync(mm.data(), d_mm, sizeof(int32_t) * 2 * nchunks, cudaMemcpyDeviceToHost, st);
+  const cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(d_ent);
+  cudaFree(d_mm);
+  if (e != cudaSuccess)
+    return cuda_fail(e, "plan_chunking", __FILE__, __LINE__);
+  std::copy(mm.begin(), mm.begin() + nchunks, col_min);
+  std::copy(mm.begin() + nchunks, mm.end(), col_max);
+  return B200_OK;
+}
+
+int b200_csr_spmv_tiles_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind, const double* d_val,
+                            double alpha, const double* d_x, double beta, double* d_y, int32_t tile_begin,
+                            int32_t tile_end, void* stream)
+{
+  B200_REQUIRE(tile_end >= 0, "bad tile range");
+  return run_spmv<double, false>(plan, d_rowptr, d_colind, d_val, nullptr, alpha, d_x, beta, d_y, nullptr, stream,
+                                 tile_begin, tile_end);
+}
+
+int b200_csr_symv_tiles_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind, const double* d_val,
+                            const double* d_diag, double alpha, const double* d_x, double* d_y,
+                            int32_t tile_begin, int32_t tile_end, void* stream)
+{
+  B200_REQUIRE(tile_end >= 0, "bad tile range");
+  return run_spmv<double, true>(plan, d_rowptr, d_colind, d_val, d_diag, alpha, d_x, 1.0, d_y, nullptr, stream,
+                                tile_begin, tile_end);
 }
 
 int b200_csr_spmv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,

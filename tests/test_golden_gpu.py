@@ -3,6 +3,7 @@ compiled code -- see make_golden.py), through the reference-shaped API (spmv_b20
 
 Tolerances are BASELINE.json's: y within 1e-12 relative L2; CG iteration counts within +-1 and the
 residual history within 1e-10 relative, iteration by iteration."""
+import functools
 import os
 
 import numpy as np
@@ -90,3 +91,60 @@ def test_cg_history_against_golden(ex, name, symmetric):
             assert dev.max() < TOL_HIST, dev.max()
     assert rel_l2(x.cpu().numpy(), g["x"]) < 1e-9
     A.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# Matrix::mult_host: host vectors in, copies pipelined against tile ranges.  Same kernels and the
+# same per-row order as mult, so general storage must be bit-identical to update + mult; the
+# symmetric kernel's adds land in another order across chunks, so the BASELINE tolerance applies.
+# ---------------------------------------------------------------------------------------------
+@functools.lru_cache(maxsize=None)
+def _host_case(kind):
+    from tests import cases
+    if kind == "random":  # columns all over the place: every chunk needs all of x, y rows free early
+        import scipy.sparse as sp
+        n = 60000
+        rng = np.random.default_rng(5)
+        i, j = rng.integers(0, n, 12 * n), rng.integers(0, n, 12 * n)
+        A = sp.coo_matrix((rng.standard_normal(12 * n), (i, j)), shape=(n, n)).tocsr()
+        A = (A + A.T + sp.eye(n) * 40.0).tocsr()
+        A.sort_indices()
+        return n, A.indptr.astype(np.int32), A.indices.astype(np.int32), A.data
+    N, rows = cases.make_problem(kind, (48, 48, 64) if kind == "lap7" else (40, 40, 48))
+    rp, col, val = rows(0, N)
+    return N, rp.astype(np.int32), col.astype(np.int32), val
+
+
+@pytest.mark.parametrize("chunks", [1, 3, 8, 64])
+@pytest.mark.parametrize("symmetric", [False, True])
+@pytest.mark.parametrize("kind", ["lap7", "lap27", "random"])
+def test_mult_host_equals_mult(ex, kind, symmetric, chunks, monkeypatch):
+    from oracle import kernels as K
+    monkeypatch.setenv("B200_HOST_CHUNKS", str(chunks))
+    n, rp, ci, v = _host_case(kind)
+    A = api.Matrix.create_matrix(ex, rp, ci, v, n, n, [], [], symmetric, api.P2P_BLOCKING)
+    rng = np.random.default_rng(3)
+    xh = torch.from_numpy(rng.standard_normal(n)).pin_memory()
+    yh = torch.full((n,), float("nan"), dtype=torch.float64).pin_memory()
+    want_dev = _mult(ex, A, xh.numpy())
+    for _ in range(3):  # repeated calls reuse the device vectors and the chunk table
+        yh.fill_(float("nan"))
+        A.mult_host(xh.numpy(), yh.numpy())
+        got = yh.numpy()
+        if symmetric:
+            assert rel_l2(got, want_dev) < TOL_Y
+        else:
+            assert np.array_equal(got, want_dev)
+    assert rel_l2(got, K.spmv(rp, ci, v, xh.numpy())) < TOL_Y  # and the oracle
+    A.close()
+
+
+def test_mult_host_pageable_and_tiny(ex):
+    """Plain numpy (pageable) vectors and the 5x5 fixture (one tile, fewer tiles than chunks)."""
+    g = np.load(os.path.join(GOLDEN, "fixture_5x5.npz"))
+    for symmetric in (False, True):
+        A = api.Matrix.create_matrix(ex, FIX_ROWPTR, FIX_COLIND, FIX_VALUES, 5, 5, [], [], symmetric, api.P2P_BLOCKING)
+        y = np.full(5, np.nan)
+        A.mult_host(np.ascontiguousarray(g["x"]), y)
+        assert rel_l2(y, g["y_general"]) < TOL_Y
+        A.close()
