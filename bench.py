@@ -273,6 +273,36 @@ def measure_cg(api, op, timer, dev, size):
     return res
 
 
+def bind_near_gpu(local_rank):
+    """N > 1: run this rank (and first-touch its pinned buffers) on the CPUs of the NUMA node its
+    GPU hangs off, so host<->device copies do not cross the socket link.  Returns a note for `config`."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local_rank]) if vis and vis.split(",")[local_rank].isdigit() else local_rank
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(idx)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:  # nvml prints an 8-digit PCI domain, sysfs a 4-digit one
+            bus = bus[4:]
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read())
+        if node < 0:
+            return "numa: single node"
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"numa: node {node} has no allowed cpus"
+        os.sched_setaffinity(0, cpus)
+        return f"numa: bound to node {node} ({len(cpus)} cpus)"
+    except Exception as e:  # no sysfs / nvml: run unbound
+        return f"numa: unbound ({type(e).__name__})"
+
+
 def run_b200(args):
     import torch
     from spmv_b200 import api
@@ -283,6 +313,7 @@ def run_b200(args):
     assert size == args.gpus or (size == 1 and args.gpus == 1), f"--gpus {args.gpus} but WORLD_SIZE={size}"
     assert torch.cuda.is_available(), "bench.py needs a GPU: there is no CPU path"
     dev = torch.device(f"cuda:{local_rank}")
+    numa = bind_near_gpu(local_rank) if size > 1 else "numa: unbound (one rank)"
     torch.cuda.set_device(dev)
     if size > 1:
         import torch.distributed as dist
@@ -315,7 +346,8 @@ def run_b200(args):
            "rows_per_gpu": op.rows, "stored_nnz_per_gpu": op.nnz_local + op.nnz_remote, "nnz_full_per_gpu": op.nnz_full(),
            "n_gpus": size, "api": "spmv_b200.api (create_laplace3d, L2GMap.update, Matrix.mult) -> libspmv_b200.so -> C ABI",
            "l2": "inputs (1.07 GB streamed per step, x and y 134 MB each) exceed the 126 MB L2; no explicit flush",
-           "GFLOPs": head["GFLOPs"]}
+           "GFLOPs": head["GFLOPs"], "host": numa,
+           "e2e_api": "Matrix.mult_host: pinned host x in, pinned host y out, copies pipelined against tile ranges"}
     op.close()
     del op
 

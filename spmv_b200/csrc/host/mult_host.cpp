@@ -7,8 +7,11 @@
 // and its y rows are final as soon as no later chunk can scatter into them.  x goes up
 // in pieces on one stream, the tile ranges run on the executor's stream as their
 // piece of x lands, finished pieces of y come down on a third stream -- both PCIe
-// directions busy at once.  Falls back to the three blocking steps whenever the
-// operator has neighbours (the halo needs all of x first) or two non-empty blocks.
+// directions busy at once.  With neighbours and an overlapping communication model
+// (local + remote block) the pages of x that the halo packs go up first, the exchange
+// and the remote block run while the first chunk is still on its way, and the local
+// chunks then add on top (beta = 1; same sum per row as Matrix::mult, operands swapped).
+// Blocking models with ghosts (one merged block) fall back to the three blocking steps.
 #include "Matrix.h"
 
 #include "L2GMap.h"
@@ -36,6 +39,9 @@ struct HostPipe {
   std::vector<void*> ev_x, ev_k, ev_y; // x piece landed, tile range done, y piece on the host (trace only)
   void* ev_start = nullptr;
   bool pipelined = false;
+  bool halo = false; // neighbours: boundary pages first, exchange + remote block, then the chunks add
+  std::vector<std::int32_t> edge; // [begin, end) pairs: the pages of x the halo packs
+  void* ev_edge = nullptr;
   bool trace = false; // B200_HOST_TRACE=1: timed events, one timeline line per call on stderr
   ~HostPipe()
   {
@@ -47,6 +53,8 @@ struct HostPipe {
       b200_event_destroy(e);
     if (ev_start)
       b200_event_destroy(ev_start);
+    if (ev_edge)
+      b200_event_destroy(ev_edge);
     if (h2d)
       b200_stream_destroy(h2d);
     if (d2h)
@@ -88,7 +96,27 @@ void Matrix<double>::mult_host(const double* x_host, double* y_host) const
     hp->y_dev = _exec->alloc<double>(static_cast<size_t>(nrows) + 1);
     const auto* blk = dynamic_cast<const CSRMatrix<double>*>(_mat_local.get());
     const bool one_block = !_mat_remote || _mat_remote->non_zeros() == 0;
-    hp->pipelined = blk && blk->op().plan() && blk->non_zeros() > 0 && nghost == 0 && one_block;
+    const bool alone = nghost == 0 && one_block && _col_map->indexbuf().empty();
+    hp->halo = !alone && _col_map->overlapping() && _mat_remote != nullptr;
+    if (hp->halo) {
+      // pages holding the entries the neighbours want; give up if that is a large part of x
+      std::vector<std::int32_t> pages;
+      for (std::int32_t i : _col_map->indexbuf())
+        pages.push_back(i / PAGE);
+      std::sort(pages.begin(), pages.end());
+      pages.erase(std::unique(pages.begin(), pages.end()), pages.end());
+      if (static_cast<std::int64_t>(pages.size()) * PAGE * 4 > nloc)
+        hp->halo = false;
+      for (size_t i = 0; hp->halo && i < pages.size();) {
+        size_t j = i;
+        while (j + 1 < pages.size() && pages[j + 1] == pages[j] + 1)
+          ++j;
+        hp->edge.push_back(pages[i] * PAGE);
+        hp->edge.push_back(std::min<std::int32_t>((pages[j] + 1) * PAGE, nloc));
+        i = j + 1;
+      }
+    }
+    hp->pipelined = blk && blk->op().plan() && blk->non_zeros() > 0 && (alone || hp->halo);
     if (hp->pipelined) {
       // Equal chunks of tiles; 8 is the measured optimum on PCIe gen5 (profiles/r01_e2e_pipeline.md:
       // fewer leaves more of the first upload / last download un-overlapped, more adds per-chunk
@@ -122,6 +150,7 @@ void Matrix<double>::mult_host(const double* x_host, double* y_host) const
       hp->y_ready[C - 1] = nrows;
       ck(b200_stream_create(&hp->h2d), "stream");
       ck(b200_stream_create(&hp->d2h), "stream");
+      ck(b200_event_create(&hp->ev_edge, 0), "event");
       hp->ev_x.assign(C, nullptr);
       hp->ev_k.assign(C, nullptr);
       const char* tr = std::getenv("B200_HOST_TRACE");
@@ -153,11 +182,25 @@ void Matrix<double>::mult_host(const double* x_host, double* y_host) const
   const auto* blk = static_cast<const CSRMatrix<double>*>(_mat_local.get());
   void* plan = blk->op().plan();
   const int C = hp.nchunks;
-  if (_symmetric) // every write of the symmetric kernel is an add
+  if (_symmetric || hp.halo) // every write below is an add
     ck(b200_memset_async(hp.y_dev, 0, sizeof(double) * static_cast<size_t>(nrows), S), "memset");
   std::int32_t x_sent = 0, y_sent = 0;
   if (hp.trace)
     ck(b200_event_record(hp.ev_start, hp.h2d), "event");
+  if (hp.halo) {
+    // the chunks below bring the same pages again (identical bytes, ~1 MB for a slab)
+    for (size_t i = 0; i + 1 < hp.edge.size(); i += 2)
+      ck(b200_memcpy_h2d_async(hp.x_dev + hp.edge[i], x_host + hp.edge[i],
+                               sizeof(double) * (hp.edge[i + 1] - hp.edge[i]), hp.h2d),
+         "h2d");
+    ck(b200_event_record(hp.ev_edge, hp.h2d), "event");
+    ck(b200_stream_wait_event(S, hp.ev_edge), "wait");
+    _col_map->update(hp.x_dev);
+    _col_map->update_finalise(hp.x_dev);
+    if (_mat_remote->non_zeros() > 0)
+      _mat_remote->mult(1, hp.x_dev, 1, hp.y_dev);
+  }
+  const double beta = hp.halo ? 1.0 : 0.0;
   for (int k = 0; k < C; ++k) {
     if (hp.x_need[k] > x_sent) {
       ck(b200_memcpy_h2d_async(hp.x_dev + x_sent, x_host + x_sent, sizeof(double) * (hp.x_need[k] - x_sent), hp.h2d),
@@ -171,7 +214,7 @@ void Matrix<double>::mult_host(const double* x_host, double* y_host) const
                                  hp.y_dev, hp.tile_bounds[k], hp.tile_bounds[k + 1], S),
          "symv tiles");
     else
-      ck(b200_csr_spmv_tiles_f64(plan, blk->rowptr(), blk->colind(), blk->values(), 1.0, hp.x_dev, 0.0, hp.y_dev,
+      ck(b200_csr_spmv_tiles_f64(plan, blk->rowptr(), blk->colind(), blk->values(), 1.0, hp.x_dev, beta, hp.y_dev,
                                  hp.tile_bounds[k], hp.tile_bounds[k + 1], S),
          "spmv tiles");
     ck(b200_event_record(hp.ev_k[k], S), "event");

@@ -145,6 +145,13 @@ def main():
                 check(np.array_equal(x.cpu().numpy(), ref["x"]), tag + ": ghost values differ after update")
                 check(rel_l2(y.cpu().numpy(), ref["y"]) < TOL_Y or np.array_equal(y.cpu().numpy(), ref["y"]),
                       tag + f": y rel err {rel_l2(y.cpu().numpy(), ref['y'])}")
+                # Matrix::mult_host: host vectors, copies pipelined (neighbours: edge pages, halo and
+                # remote block first, local chunks add on top) -- same values as update + mult
+                yh = np.full(inp["nrows_local"], np.nan)
+                for _ in range(2):
+                    A.mult_host(np.ascontiguousarray(x_fn(inp["r0"], inp["r1"])), yh)
+                check(np.array_equal(yh, y.cpu().numpy()) if not sym else rel_l2(yh, y.cpu().numpy()) < TOL_Y,
+                      tag + f": mult_host vs mult rel err {rel_l2(yh, y.cpu().numpy())}")
                 if want_cg:
                     b = torch.from_numpy(ref["b"]).to(dev)
                     xs = torch.zeros_like(b)
@@ -180,6 +187,27 @@ def main():
                       tag + ": sizes differ")
                 A0.close()
                 A1.close()
+
+    # mult_host on slabs big enough for several chunks and distinct edge pages
+    if mode == "gpu":
+        for st, sym, cm in ((7, True, api.P2P_NONBLOCKING), (27, False, api.P2P_NONBLOCKING),
+                            (27, False, api.COLLECTIVE_NONBLOCKING), (7, False, api.P2P_BLOCKING)):
+            A = api.create_laplace3d(ex, 64, 48, 40 * size, st, sym, cm)
+            m, cmap = A.rows(), A.col_map()
+            xh = np.random.default_rng(11 + rank).standard_normal(m)
+            x = torch.zeros(cmap.local_size() + cmap.num_ghosts(), dtype=torch.float64, device=dev)
+            x[:m] = torch.from_numpy(xh).to(dev)
+            y = torch.full((m,), float("nan"), dtype=torch.float64, device=dev)
+            cmap.update(x)
+            A.mult(x, y)
+            ex.synchronize()
+            yh = np.full(m, np.nan)
+            for _ in range(3):
+                A.mult_host(xh, yh)
+            err = rel_l2(yh, y.cpu().numpy())
+            check(np.array_equal(yh, y.cpu().numpy()) if not sym else err < TOL_Y,
+                  f"mult_host slab st={st} sym={sym} cm={cm} size={size}: rel err {err}")
+            A.close()
 
     # read_petsc + create_A builders over the multi-process transport
     N, rows = cases.make_problem("powerlaw", 3000)
