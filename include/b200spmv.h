@@ -82,8 +82,10 @@ B200_API int b200_csr_plan_info(void* plan, int32_t* num_tiles, int32_t* max_row
 /* Tuning hook (bench sweeps, tests).  variant 0 = persistent CTAs with a bulk-async staged
  * ring, walk chosen from the row-length histogram (default); 1 = one tile per CTA staged
  * with plain loads; 2..5 = variant 0 with the walk forced: 2 one thread per row in chunks
- * of 16 entries, 3 two-phase stream walk, 4 chunks of 8, 5 chunks of 4.  consumer_warps is
- * 8 or 16.  Re-partitions the tiles (needs the same d_rowptr the plan was created with).
+ * of 16 entries, 3 two-phase stream walk, 4 chunks of 8, 5 chunks of 4, 6 warp-private
+ * stream walk (general storage; each consumer warp owns a plan-time segment of the tile, no
+ * CTA barrier; symmetric plans fall back to 3).  consumer_warps is 8 or 16.  Re-partitions
+ * the tiles (needs the same d_rowptr the plan was created with).
  * Defaults also read B200_SPMV_{VARIANT,TILE_BYTES,STAGES,CWARPS,CTAS} from the
  * environment at plan creation. */
 B200_API int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int tile_bytes,

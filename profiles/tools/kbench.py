@@ -43,17 +43,30 @@ def powerlaw(a, dev):
     x = torch.from_numpy(synth.bump_vector(N, 0, N)).to(dev)
     y = torch.empty(N, dtype=torch.float64, device=dev)
     nbytes = 12 * nnz + 4 * (N + 1) + 16 * N
+    if a.tune:
+        plan.tune(*[int(t) for t in a.tune.split(",")])
     ms = timeit(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y), a)
     info = plan.info()
     print(f"powerlaw rows={N} nnz={nnz} max_row={info['max_row_len']} tiles={info['num_tiles']} (plan defaults): "
           f"{ms:.4f} ms  {nbytes / ms / 1e6:.1f} GB/s algorithmic", flush=True)
     want = torch.sparse_csr_tensor(rp_d.long(), ci_d.long(), v_d, size=(N, N)).matmul(x)
     print("  rel err vs torch.sparse:", float((y - want).norm() / want.norm()), flush=True)
-    for variant in (2, 3, 4):
-        for tb, cw, ct in ((24576, 8, 3), (24576, 16, 2), (49152, 8, 2), (49152, 16, 2), (32768, 8, 3)):
-            plan.tune(variant, tb, 2, cw, ct)
+    if a.tune:
+        return
+    variants = [int(v) for v in os.environ.get("KB_VARIANTS", "2,3,4,6").split(",")]
+    for variant in variants:
+        shapes = [(24576, 2, 8, 3), (24576, 2, 16, 2), (49152, 2, 8, 2), (49152, 2, 16, 2), (32768, 2, 8, 3)]
+        if variant in (3, 6):
+            shapes += [(16384, 2, 16, 2), (16384, 2, 16, 3), (24576, 2, 16, 3), (16384, 3, 16, 3), (24576, 3, 16, 2),
+                       (24576, 3, 8, 4), (12288, 2, 16, 3), (12288, 3, 16, 3), (49152, 3, 16, 1), (20480, 2, 16, 3)]
+        for tb, stg, cw, ct in shapes:
+            plan.tune(variant, tb, stg, cw, ct)
             ms = timeit(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y), a)
-            print(f"  variant={variant} tile={tb} cw={cw} ctas={ct}: {ms:.4f} ms  {nbytes / ms / 1e6:.1f} GB/s", flush=True)
+            y.fill_(float("nan"))
+            K.spmv(plan, rp_d, ci_d, v_d, x, y)
+            err = float((y - want).norm() / want.norm())
+            print(f"  variant={variant} tile={tb} stages={stg} cw={cw} ctas={ct}: {ms:.4f} ms  {nbytes / ms / 1e6:.1f} GB/s"
+                  f"  err {err:.1e}", flush=True)
 
 
 def main():
@@ -62,6 +75,7 @@ def main():
     ap.add_argument("--n", type=int, default=256)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--tune", default="", help="powerlaw: variant,tile_bytes,stages,cwarps,ctas -- time only this shape")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)

@@ -68,6 +68,7 @@ struct Plan {
   int32_t consumer_warps = 0;
   int32_t ctas_per_sm = 0;
   int32_t* d_tile_meta = nullptr; // 2*(num_tiles+1) ints
+  int32_t* d_warp_rows = nullptr; // WALK_SEG: num_tiles*(consumer_warps+1) row offsets
   int32_t max_row_len = 0;
   int64_t hist[32] = {0};
   int32_t* d_rowlist = nullptr;    // ids of the non-empty rows, ascending (sparse-row blocks only)

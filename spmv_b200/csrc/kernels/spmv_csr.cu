@@ -52,6 +52,8 @@ namespace b200
 constexpr int WALK_ROW16 = 0, WALK_STREAM = 1, WALK_ROW8 = 2, WALK_ROW4 = 3;
 // ...S: no row is longer than one chunk, so the chunk loop is gone
 constexpr int WALK_ROW8S = 4, WALK_ROW4S = 5;
+// segmented-scan walk for irregular rows (general storage): entry-parallel, warp-private, no CTA barrier
+constexpr int WALK_SEG = 6;
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
 constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
 constexpr int MAX_STAGE_BYTES = 96 * 1024;
@@ -78,6 +80,7 @@ struct SpmvArgs {
   T alpha;
   T beta;
   const int32_t* tile_meta;
+  const int32_t* warp_rows; // WALK_SEG: (CW+1) row offsets per tile, the consumer warps' segments
   int32_t tile0;     // first tile of this launch (tile sub-ranges: pipelined host-vector SpMV)
   int32_t num_tiles; // end of the tile range
   int32_t stage_bytes;
@@ -390,6 +393,152 @@ __device__ __forceinline__ dd walk_direct(const SpmvArgs<T>& a, int r0, int nrow
   return dot;
 }
 
+// Rows too long for a stage, straight from global memory, by ALL consumer warps of the
+// CTA: every thread takes entries rs + tid + k*nthreads, four gathers in flight each, then
+// warp sums -> shared -> one thread adds them in warp order.  (One warp walking such a row
+// alone is a chain of ~125 dependent global round trips for 4000 entries, ~0.15 ms: longer
+// than the rest of the kernel, and the CTA that drew the row held everyone up.)
+template <typename T, bool SYM, bool DOT>
+__device__ __forceinline__ dd walk_direct_cta(const SpmvArgs<T>& a, int r0, int nrows, int tid, int nthreads,
+                                              int warp, int nwarps, int lane, int bar_id, double* s_part)
+{
+  constexpr int U = 4;
+  dd dot = {0.0, 0.0};
+  for (int k = 0; k < nrows; ++k) {
+    const int r = r0 + k;
+    const int rs = __ldg(a.rowptr + r), re = __ldg(a.rowptr + r + 1);
+    T xi = 0;
+    if (SYM)
+      xi = __ldg(a.x + r);
+    T part = 0;
+    for (int j0 = rs + tid; j0 < re; j0 += nthreads * U) {
+      int c[U];
+      T v[U], xv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = j0 + u * nthreads;
+        const bool ok = j < re;
+        c[u] = ok ? __ldg(a.colind + j) : 0;
+        v[u] = ok ? __ldg(a.val + j) : T(0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        xv[u] = j0 + u * nthreads < re ? __ldg(a.x + c[u]) : T(0);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        part = fma(v[u], xv[u], part);
+        if (SYM && j0 + u * nthreads < re)
+          red_add(a.y + c[u], a.alpha * v[u] * xi);
+      }
+    }
+    part = warp_sum(part);
+    if (lane == 0)
+      s_part[warp] = (double)part;
+    named_bar_sync(bar_id, nthreads);
+    if (tid == 0) {
+      double sum = 0.0;
+      for (int w = 0; w < nwarps; ++w)
+        sum += s_part[w];
+      T tot = (T)sum;
+      if (SYM)
+        tot += __ldg(a.diag + r) * xi;
+      const T out = store_row<T, SYM>(a, r, tot);
+      if (DOT)
+        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+    }
+    named_bar_sync(bar_id, nthreads); // s_part is free again
+  }
+  return dot;
+}
+
+// ---------------------------------------------------------------------------
+// Warp-private stream walk (WALK_SEG; general storage, irregular row lengths).
+// The stream walk's two phases -- products by entry, sums by row -- but each consumer
+// warp owns a SEGMENT of the tile: the rows that start in its equal share of the
+// tile's entries, cut at plan time (plan_warp_rows_kernel; a.warp_rows holds CW+1 row
+// offsets per tile).  Phase 1, lanes over the segment's entries: product with the
+// gathered x, written back over the staged value, four gathers in flight per lane.
+// Phase 2, lanes over its rows: left-to-right sum of the products (the reference's
+// order, so rows <= 32 entries stay bit-identical); longer rows by the whole warp.
+// Only __syncwarp between the phases: no warp waits for another until the stage is
+// released, so with 3 stages a warp that drew a 1000-entry row does not hold up the
+// CTA (the two CTA-wide barriers per tile were 11 of 30 stall cycles per issue in
+// the stream walk on the power-law matrix, profiles/r01_powerlaw_walks.md).
+// ---------------------------------------------------------------------------
+template <typename T, bool DOT>
+__device__ __forceinline__ dd walk_seg(const SpmvArgs<T>& a, unsigned char* stage, const StageMeta* m, int ka,
+                                       int kb, int lane)
+{
+  constexpr int U = 4;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
+  const TileLayout<T, LAY_PLAIN> L(r0, nrows, lo, hi);
+  T* sv = reinterpret_cast<T*>(stage) + (lo - L.lo_v);                       // sv[j - lo]
+  const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c); // sc[j - lo]
+  const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r);
+  dd dot = {0.0, 0.0};
+  ka = min(ka, nrows); // the producer may have staged a prefix of the tile's rows only
+  kb = min(kb, nrows);
+  if (ka >= kb)
+    return dot;
+  const int ea = sr[ka] - lo, eb = sr[kb] - lo;
+
+  for (int j0 = ea + lane; j0 < eb; j0 += 32 * U) {
+    int c[U];
+    T v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int j = j0 + u * 32;
+      const bool ok = j < eb;
+      c[u] = ok ? sc[j] : 0;
+      v[u] = ok ? sv[j] : T(0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (j0 + u * 32 < eb)
+        v[u] = mul_rn(v[u], __ldg(a.x + c[u]));
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (j0 + u * 32 < eb)
+        sv[j0 + u * 32] = v[u];
+  }
+  __syncwarp();
+
+  for (int k0 = ka; k0 < kb; k0 += 32) {
+    const int k = k0 + lane;
+    int rs = 0, re = 0;
+    if (k < kb) {
+      rs = sr[k] - lo;
+      re = sr[k + 1] - lo;
+    }
+    const bool is_long = re - rs > SHORT_ROW;
+    if (k < kb && !is_long) {
+      T sum = T(0);
+      for (int j = rs; j < re; ++j)
+        sum = add_rn(sum, sv[j]);
+      const T out = store_row<T, false>(a, r0 + k, sum);
+      if (DOT)
+        dd_add_prod(dot, (double)__ldg(a.x + r0 + k), (double)out);
+    }
+    unsigned todo = __ballot_sync(FULL, is_long);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int qs = __shfl_sync(FULL, rs, src), qe = __shfl_sync(FULL, re, src);
+      T part = T(0);
+      for (int j = qs + lane; j < qe; j += 32)
+        part += sv[j];
+      part = warp_sum(part);
+      if (lane == 0) {
+        const T out = store_row<T, false>(a, r0 + k0 + src, part);
+        if (DOT)
+          dd_add_prod(dot, (double)__ldg(a.x + r0 + k0 + src), (double)out);
+      }
+    }
+  }
+  return dot;
+}
+
 // ---------------------------------------------------------------------------
 // Variant 0: persistent CTAs, bulk-async staged ring, warp-specialised.
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
@@ -403,7 +552,7 @@ __device__ __forceinline__ void fence_proxy_async_smem()
 template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
-  constexpr int LAY = SYM ? (WALK == WALK_STREAM ? LAY_DXP : LAY_DX) : LAY_PLAIN;
+  constexpr int LAY = SYM ? ((WALK == WALK_STREAM || WALK == WALK_SEG) ? LAY_DXP : LAY_DX) : LAY_PLAIN;
   constexpr int CHUNK = (WALK == WALK_ROW4 || WALK == WALK_ROW4S) ? 4 : ((WALK == WALK_ROW8 || WALK == WALK_ROW8S) ? 8 : 16);
   constexpr bool SINGLE = WALK == WALK_ROW4S || WALK == WALK_ROW8S;
   extern __shared__ __align__(128) unsigned char smem[];
@@ -429,8 +578,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
 
   if (warp == CW) {
     if (lane == 0) {
-      for (int it = 0; it < my_tiles; ++it) {
-        const int s = it % stages, use = it / stages;
+      for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
         if (use > 0)
           mbar_wait(empty + s, (use - 1) & 1);
         const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
@@ -473,13 +621,34 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
   }
 
   dd dot = {0.0, 0.0};
-  for (int it = 0; it < my_tiles; ++it) {
-    const int s = it % stages, use = it / stages;
+  // Two spellings of the same loop.  ptxas schedules the 16-entry row walk ~20% worse (27-point:
+  // 0.85 -> 1.04 ms) with the incremental stage counters and the CTA-wide direct walk in the loop
+  // body, and the 8-entry general walk ~2% better (7-point: 0.257 -> 0.251 ms), A/B-measured in
+  // profiles/r01_powerlaw_walks.md; the irregular walks need the CTA-wide direct walk.
+  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || WALK == WALK_SEG || (!SYM && CHUNK == 8);
+  for (int it = 0, cs = 0, cu = 0; it < my_tiles; ++it) {
+    int s, use;
+    if constexpr (CTA_DIRECT) {
+      s = cs, use = cu;
+      cs = cs + 1 == stages ? 0 : cs + 1;
+      cu += cs == 0;
+    } else {
+      s = it % stages, use = it / stages;
+    }
+    int seg_a = 0, seg_b = 0; // this warp's rows of the tile (their load overlaps the wait)
+    if (WALK == WALK_SEG && !SYM) {
+      const int32_t* wr = a.warp_rows + (size_t)(a.tile0 + blockIdx.x + it * gridDim.x) * (CW + 1) + warp;
+      seg_a = __ldg(wr);
+      seg_b = __ldg(wr + 1);
+    }
     mbar_wait(full + s, use & 1);
     StageMeta* m = meta + s;
     const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
     if (ns > 0) {
-      if (WALK == WALK_STREAM) {
+      if (WALK == WALK_SEG && !SYM) {
+        dot = dd_merge(dot, walk_seg<T, DOT>(a, smem + (size_t)s * sb, m, seg_a, seg_b, lane));
+        fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
+      } else if (WALK == WALK_STREAM || WALK == WALK_SEG) {
         dot = dd_merge(dot, walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32,
                                                            warp, CW, lane, 1));
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
@@ -488,8 +657,13 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
                                                                                threadIdx.x, CW * 32, warp, CW, lane, 1));
       }
     }
-    if (ns < nrows)
-      dot = dd_merge(dot, walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane));
+    if (ns < nrows) {
+      if constexpr (CTA_DIRECT)
+        dot = dd_merge(dot, walk_direct_cta<T, SYM, DOT>(a, r0 + ns, nrows - ns, threadIdx.x, CW * 32, warp, CW,
+                                                         lane, 1, s_warp));
+      else
+        dot = dd_merge(dot, walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane));
+    }
     __syncwarp();
     if (lane == 0)
       mbar_arrive(empty + s);
@@ -648,6 +822,31 @@ __global__ void plan_tiles_kernel(const int32_t* __restrict__ rowptr, int rows, 
   meta[2 * b + 1] = rowptr[lo];
 }
 
+// WALK_SEG: cut every tile into `cw` segments of (nearly) equal entry counts at row boundaries.
+// out[t*(cw+1) + w] = first row of tile t (as an offset from the tile's first row) that starts at
+// or after entry lo + n*w/cw; segment w = rows [out[w], out[w+1]).
+__global__ void plan_warp_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ meta,
+                                      int num_tiles, int cw, int32_t* __restrict__ out)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)num_tiles * (cw + 1))
+    return;
+  const int t = (int)(i / (cw + 1)), w = (int)(i % (cw + 1));
+  const int r0 = meta[2 * t], lo = meta[2 * t + 1], r1 = meta[2 * t + 2], hi = meta[2 * t + 3];
+  const int target = lo + (int)((long long)(hi - lo) * w / cw);
+  int x0 = r0, x1 = r1; // first row in [r0, r1] with rowptr[row] >= target
+  if (w == cw)
+    x0 = r1;
+  while (x0 < x1) {
+    const int mid = x0 + ((x1 - x0) >> 1);
+    if (rowptr[mid] >= target)
+      x1 = mid;
+    else
+      x0 = mid + 1;
+  }
+  out[i] = x0 - r0;
+}
+
 __global__ void plan_hist_kernel(const int32_t* __restrict__ rowptr, int rows,
                                  unsigned long long* __restrict__ hist, int* __restrict__ max_len)
 {
@@ -713,6 +912,10 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
     B200_CUDA(cudaFree(p->d_tile_meta));
     p->d_tile_meta = nullptr;
   }
+  if (p->d_warp_rows) {
+    B200_CUDA(cudaFree(p->d_warp_rows));
+    p->d_warp_rows = nullptr;
+  }
   p->num_tiles = 0;
   if (p->nnz == 0 || p->rows == 0 || d_rowptr == nullptr)
     return B200_OK;
@@ -721,7 +924,7 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   p->w_row = 4;
   if (p->symmetric && p->variant == 0) {
     p->w_row = 20; // rowptr + diagonal + x
-    if (p->walk == WALK_STREAM)
+    if (p->walk == WALK_STREAM || p->walk == WALK_SEG)
       p->w_entry = 20; // value + column + product
   }
   const long long total = (long long)p->w_entry * p->nnz + (long long)p->w_row * p->rows;
@@ -734,6 +937,13 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   plan_tiles_kernel<<<blocks, threads, 0, st>>>(d_rowptr, p->rows, p->nnz, p->num_tiles,
                                                 p->tile_bytes, p->w_entry, p->w_row, p->d_tile_meta);
   B200_LAUNCH_CHECK();
+  if (p->walk == WALK_SEG && !p->symmetric && p->variant == 0) {
+    const long long n = nt * (p->consumer_warps + 1);
+    B200_CUDA(cudaMalloc(&p->d_warp_rows, sizeof(int32_t) * (size_t)n));
+    plan_warp_rows_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, st>>>(
+        d_rowptr, p->d_tile_meta, p->num_tiles, p->consumer_warps, p->d_warp_rows);
+    B200_LAUNCH_CHECK();
+  }
   return B200_OK;
 }
 
@@ -771,6 +981,7 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* cw, int* cta
     *tile_bytes = 24 * 1024, *cw = 8, *ctas = p->symmetric ? 3 : 4;
     break;
   case WALK_STREAM:
+  case WALK_SEG:
     *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
     break;
   default:
@@ -778,12 +989,19 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* cw, int* cta
   }
 }
 
+// b200_csr_plan_tune's variant -> forced walk (-1: chosen from the histogram)
+static int walk_of_variant(int variant)
+{
+  return variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
+}
+
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant >= 0 && variant <= 5, "variant must be 0..5");
+  B200_REQUIRE(variant >= 0 && variant <= 6, "variant must be 0..6");
   // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
-  // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4
-  p->walk_forced = variant >= 2 ? variant - 2 : -1;
+  // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4;
+  // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM)
+  p->walk_forced = walk_of_variant(variant);
   if (variant >= 2)
     variant = 0;
   B200_REQUIRE(tile_bytes >= 1024 && tile_bytes + 2048 <= MAX_STAGE_BYTES, "tile_bytes out of range");
@@ -851,6 +1069,11 @@ static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st
   switch (p.walk) {
   case WALK_STREAM:
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
+  case WALK_SEG:
+    if constexpr (SYM) // the scan walk is general-storage only
+      return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
+    else
+      return launch_pipe_cw<T, SYM, DOT, false, WALK_SEG>(p, a, st);
   case WALK_ROW8:
     if (p.max_row_len <= 8)
       return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW8S>(p, a, st);
@@ -958,6 +1181,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.alpha = alpha;
   a.beta = beta;
   a.tile_meta = p.d_tile_meta;
+  a.warp_rows = p.d_warp_rows;
   a.tile0 = ranged ? tile_begin : 0;
   a.num_tiles = ranged ? tile_end : p.num_tiles;
   a.stage_bytes = p.stage_bytes;
@@ -1080,7 +1304,7 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   // the histogram picks the walk and its launch shape (environment overrides for
   // sweeps), the walk fixes the stage weights, the weights cut the tiles
   const int variant = env_int("B200_SPMV_VARIANT", 0);
-  p->walk_forced = variant >= 2 ? variant - 2 : -1;
+  p->walk_forced = walk_of_variant(variant);
   plan_choose_walk(p);
   int d_tile, d_cw, d_ctas;
   plan_default_shape(p, &d_tile, &d_cw, &d_ctas);
@@ -1102,6 +1326,7 @@ int b200_csr_plan_destroy(void* plan)
   if (!p)
     return B200_OK;
   cudaFree(p->d_tile_meta);
+  cudaFree(p->d_warp_rows);
   cudaFree(p->d_rowlist);
   cudaFree(p->d_partials);
   cudaFree(p->d_counter);

@@ -28,6 +28,13 @@ VARIANTS = [
     dict(variant=4, tile_bytes=16384, stages=2, consumer_warps=8, ctas_per_sm=3),
     dict(variant=5, tile_bytes=24576, stages=2, consumer_warps=16, ctas_per_sm=2),
 ]
+# 6 = segmented-scan walk: pairwise row sums, within tolerance but not bit-identical to the
+# reference's left-to-right loop, so it joins the tolerance tests only
+SEG_VARIANTS = [
+    dict(variant=6, tile_bytes=24576, stages=2, consumer_warps=16, ctas_per_sm=2),
+    dict(variant=6, tile_bytes=2048, stages=3, consumer_warps=8, ctas_per_sm=2),
+    dict(variant=6, tile_bytes=49152, stages=4, consumer_warps=8, ctas_per_sm=1),
+]
 
 
 def dev_csr(rowptr, colind, values, dev, dtype=torch.float64):
@@ -115,7 +122,7 @@ def test_general_alpha_beta(cuda, alpha, beta):
     assert rel_l2(y, OK.spmv(A.indptr, A.indices, A.data, x, alpha, beta, y0)) < TOL
 
 
-@pytest.mark.parametrize("tune", VARIANTS)
+@pytest.mark.parametrize("tune", VARIANTS + SEG_VARIANTS)
 def test_powerlaw_irregular(cuda, tune):
     n = 60000
     rp, col, val = synth.powerlaw_rows(n, 0, n, band=2048)
@@ -126,7 +133,7 @@ def test_powerlaw_irregular(cuda, tune):
     assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL
 
 
-@pytest.mark.parametrize("tune", VARIANTS)
+@pytest.mark.parametrize("tune", VARIANTS + SEG_VARIANTS)
 def test_huge_row_and_empty_rows(cuda, tune):
     # rows: empty, short, one row far larger than a stage (direct path), empty tail
     rng = np.random.default_rng(3)
@@ -181,7 +188,7 @@ def test_zero_rows_and_zero_nnz(cuda):
     assert np.array_equal(y, np.zeros(10))
 
 
-@pytest.mark.parametrize("tune", VARIANTS)
+@pytest.mark.parametrize("tune", VARIANTS + SEG_VARIANTS[:1])
 def test_laplace_symmetric(cuda, tune):
     n1 = 24
     N = n1 ** 3
@@ -237,6 +244,30 @@ def test_gather_scatter(cuda):
     accd = torch.from_numpy(acc).to(cuda)
     K.scatter_add(torch.from_numpy(idx).to(cuda), torch.from_numpy(src).to(cuda), accd)
     assert rel_l2(accd.cpu().numpy(), want) < 1e-13
+
+
+@pytest.mark.parametrize("tune", SEG_VARIANTS)
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (1.0, 1.0), (-2.0, 0.25)])
+def test_segmented_scan_walk(cuda, tune, alpha, beta):
+    """Rows of every length class in one matrix (empty, 1, <=32, hundreds, thousands -- longer than
+    a warp's share and than a whole small tile), alpha/beta, and the stencil case where the other
+    walks are bit-exact."""
+    rng = np.random.default_rng(12)
+    ncols = 50000
+    lens = np.concatenate([rng.integers(0, 3, 300), rng.integers(1, 33, 300), [700, 0, 0, 2500, 1, 33, 64, 31],
+                           np.minimum((4.0 / np.sqrt(1.0 - rng.random(2000))).astype(np.int64), 4096), [0, 5000, 0]])
+    rp = np.zeros(len(lens) + 1, dtype=np.int64)
+    np.cumsum(lens, out=rp[1:])
+    col = np.concatenate([np.sort(rng.choice(ncols, size=int(l), replace=False)) for l in lens]).astype(np.int64)
+    val = rng.standard_normal(rp[-1])
+    x, y0 = rng.standard_normal(ncols), rng.standard_normal(len(lens))
+    y, _ = run_general(cuda, rp, col, val, x, ncols, alpha, beta, y0.copy(), tune=tune)
+    assert rel_l2(y, OK.spmv(rp, col, val, x, alpha, beta, y0)) < TOL
+    n1 = 16
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    x = np.random.default_rng(0).standard_normal(n1 ** 3)
+    y, _ = run_general(cuda, rp, col, val, x, n1 ** 3, tune=tune)
+    assert rel_l2(y, OK.spmv(rp, col, val, x)) < 1e-14
 
 
 def test_dot_deterministic(cuda):
