@@ -34,6 +34,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nz", type=int, default=NZ_PER_GPU, help="z-planes per GPU (default 256)")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling (BASELINE configs[2]): the 256^3 grid split over the GPUs, nz = 256 / N")
     ap.add_argument("--no-extras", action="store_true", help="skip the 'also' measurements and cpu_baseline")
     return ap.parse_args()
 
@@ -326,6 +328,9 @@ def run_b200(args):
     timer = Timer(size, dev)
     peak, peak_src = peak_hbm()
     nz = args.nz
+    if args.strong:
+        assert NZ_PER_GPU % size == 0, "--strong needs N to divide 256"
+        nz = NZ_PER_GPU // size
 
     # ---- headline: BASELINE configs[1], symmetric-storage 7-point SpMV -------------------
     op = Operator(api, ex, dev, rank, size, nz, 7, True)
@@ -375,7 +380,8 @@ def run_b200(args):
         return
     line = {
         "metric": "spmv_algorithmic_GBps", "value": head["GBps"], "unit": "GB/s", "n_gpus": size, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong" if args.strong else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "e2e": head["e2e"],
         "gpu_launches": head_launches, "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",

@@ -238,6 +238,21 @@ B200_API int b200_gen_laplace3d_fill(int nx, int ny, int64_t nzg, int64_t z0, in
                             double* d_val_local, double* d_diag, const int32_t* d_rowptr_remote,
                             int32_t* d_colind_remote, double* d_val_remote, void* stream);
 
+/* ---- scalar allreduce over peer memory: the MPI_Allreduce on device scalars of the CG loop
+ *      (cg.cpp:49,65,75; cuda/cg.cuda.cu:90,112,133), as one 32-thread kernel that stores into
+ *      every rank's IPC-mapped mailbox over NVLink and spins on its own -- no NCCL kernel, same
+ *      bits on every rank (sum in rank order).  Setup: each rank b200_ipc_alloc's a mailbox of
+ *      b200_peer_reduce_mailbox_bytes(world), the handles are exchanged by the host, every rank
+ *      opens the others' (b200_ipc_open) and passes the `world` device pointers (own one at
+ *      [rank]) to b200_peer_reduce_create, then a host barrier.  All ranks must call the
+ *      allreduce in the same order.  ctx == NULL: single rank, no-op. ------------------------ */
+#define B200_PEER_REDUCE_MAX_RANKS 16
+#define B200_PEER_REDUCE_MAX_COUNT 4
+B200_API int b200_peer_reduce_mailbox_bytes(int32_t world, size_t* num_bytes);
+B200_API int b200_peer_reduce_create(void** ctx, int32_t rank, int32_t world, void* const* d_mailboxes, void* stream);
+B200_API int b200_peer_reduce_destroy(void* ctx);
+B200_API int b200_peer_allreduce_sum_f64(void* ctx, double* d_inout, int32_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -75,6 +75,12 @@ public:
   /// what this rank SENDS in update() per neighbour (slices of the packed buffer)
   const std::vector<std::int32_t>& recv_count() const { return _recv_count; }
   const std::vector<std::int32_t>& recv_offset() const { return _recv_offset; }
+  /// Context for b200_peer_allreduce_sum_f64 over this map's communicator (nullptr: one rank,
+  /// or peer memory unavailable -- use the NCCL allreduce)
+  void* peer_reduce() const { return _ar_ctx; }
+  /// Sum n <= 4 device doubles over the communicator, in place, on the executor's stream
+  /// (peer-memory kernel if set up and !force_nccl, else ncclAllReduce).  Collective.
+  void allreduce_sum(double* d_val, int n, bool force_nccl = false) const;
   /// owner-local indices to pack, neighbour by neighbour (host copy of _indexbuf)
   const std::vector<std::int32_t>& indexbuf() const { return _indexbuf_host; }
   CommunicationModel communication_model() const { return _cm; }
@@ -111,6 +117,8 @@ private:
   // Double buffering is enough: a neighbour can only be one epoch ahead of me, because
   // its next push is stream-ordered after its wait for my previous one.
   void setup_peer_halo();
+  void setup_peer_reduce(bool peers_usable);
+  void teardown_peer_reduce();
   template <typename T>
   void exchange_forward_peer(T* vec_data, void* stream) const;
   bool _peer_ok = false;
@@ -120,6 +128,10 @@ private:
   std::vector<size_t> _peer_slot_bytes;
   std::vector<std::int64_t> _land;   // per neighbour: element offset of my slice in its ghost tail
   mutable std::uint32_t _epoch = 0;
+  // scalar allreduce over peer memory (CG): my mailbox, everyone's as mapped here, device descriptor
+  char* _ar_box = nullptr;
+  std::vector<void*> _ar_boxes;
+  void* _ar_ctx = nullptr;
 };
 
 } // namespace spmv

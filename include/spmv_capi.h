@@ -53,6 +53,9 @@ SPMVH_API int spmvh_l2g_global_to_local(void* map, int64_t global_index, int32_t
 SPMVH_API int spmvh_l2g_update_f64(void* map, double* d_vec);
 SPMVH_API int spmvh_l2g_update_finalise_f64(void* map, double* d_vec);
 SPMVH_API int spmvh_l2g_reverse_update_f64(void* map, double* d_vec);
+/* Sum d_val[0..n) (n <= 4) over the map's communicator on the executor's stream, as the CG loop
+ * does: use_nccl == 0 -> peer-memory kernel when the map has one (else NCCL), != 0 -> NCCL. */
+SPMVH_API int spmvh_l2g_allreduce_f64(void* map, double* d_val, int32_t n, int use_nccl);
 
 /* ---- Matrix<double> builders ---- */
 SPMVH_API int spmvh_matrix_create(void** mat, void* exec, const int32_t* rowptr, const int32_t* colind,

@@ -59,6 +59,7 @@ _SIG = {
     "spmvh_matrix_block_copy": [_p, _int, _p, _p, _p, _p],
     "spmvh_matrix_mult_f64": [_p, _p, _p],
     "spmvh_matrix_mult_host_f64": [_p, _p, _p],
+    "spmvh_l2g_allreduce_f64": [_p, _p, _i32, C.c_int],
     "spmvh_matrix_tune": [_p, _int, _int, _int, _int, _int, _int],
     "spmvh_cg": [_p, _p, _p, _p, _int, _f64, _p, _int, C.POINTER(_int)],
     "spmvh_write_petsc_matrix": [C.c_char_p, _i32, _i32, _p, _p, _p],
@@ -350,6 +351,10 @@ class L2GMap:
 
     def reverse_update(self, vec):
         _ck(host_lib().spmvh_l2g_reverse_update_f64(self.h, _dev_ptr(vec)))
+
+    def allreduce_sum(self, vec, nccl=False):
+        """Sum the (<= 4) doubles of `vec` over the ranks, in place, on the executor's stream."""
+        _ck(host_lib().spmvh_l2g_allreduce_f64(self.h, _dev_ptr(vec), int(vec.numel()), int(bool(nccl))))
 
     def close(self):
         if self.h:

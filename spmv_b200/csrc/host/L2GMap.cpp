@@ -194,6 +194,73 @@ void L2GMap::setup_peer_halo()
       b200_free(_stage);
     _stage = nullptr;
   }
+  setup_peer_reduce(_peer_ok);
+}
+//-----------------------------------------------------------------------------
+// Collective.  Mailboxes for the scalar allreduce of the CG loop (b200_peer_allreduce_sum_f64):
+// every rank maps every other rank's.  Falls back to NCCL (context stays null) if any rank
+// cannot, if peer memory was refused for the halo, or with B200_ALLREDUCE=nccl.
+void L2GMap::setup_peer_reduce(bool peers_usable)
+{
+  int mpi_size = 0;
+  CHECK_MPI(MPI_Comm_size(_comm, &mpi_size));
+  const char* mode = std::getenv("B200_ALLREDUCE");
+  int ok = peers_usable && mpi_size <= B200_PEER_REDUCE_MAX_RANKS && !(mode && std::strcmp(mode, "nccl") == 0);
+  struct Card {
+    char handle[B200_IPC_HANDLE_BYTES];
+    std::int64_t ok;
+  };
+  Card mine;
+  std::memset(&mine, 0, sizeof(mine));
+  size_t bytes = 0;
+  void* box = nullptr;
+  if (ok && (b200_peer_reduce_mailbox_bytes(mpi_size, &bytes) != B200_OK || b200_ipc_alloc(&box, bytes, mine.handle) != B200_OK))
+    ok = 0;
+  _ar_box = static_cast<char*>(box);
+  mine.ok = ok;
+  std::vector<Card> cards(mpi_size);
+  CHECK_MPI(MPI_Allgather(&mine, static_cast<int>(sizeof(Card)), MPI_CHAR, cards.data(), static_cast<int>(sizeof(Card)),
+                          MPI_CHAR, _comm));
+  for (const Card& c : cards)
+    ok = ok && c.ok != 0;
+  _ar_boxes.assign(mpi_size, nullptr);
+  if (ok) {
+    for (int q = 0; q < mpi_size && ok; ++q) {
+      if (q == _mpi_rank)
+        _ar_boxes[q] = _ar_box;
+      else if (b200_ipc_open(&_ar_boxes[q], cards[q].handle) != B200_OK)
+        ok = 0;
+    }
+  }
+  if (ok && b200_peer_reduce_create(&_ar_ctx, _mpi_rank, mpi_size, _ar_boxes.data(), as_b200(_exec)->get_cuda_stream()) != B200_OK)
+    ok = 0;
+  int all_ok = 0;
+  CHECK_MPI(MPI_Allreduce(&ok, &all_ok, 1, MPI_INT, MPI_MIN, _comm)); // also the barrier after the mailboxes were zeroed
+  if (!all_ok)
+    teardown_peer_reduce();
+}
+void L2GMap::allreduce_sum(double* d_val, int n, bool force_nccl) const
+{
+  const B200Executor* gpu = as_b200(_exec);
+  if (!gpu)
+    throw std::runtime_error("L2GMap::allreduce_sum needs the B200 executor");
+  detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  if (_ar_ctx && !force_nccl)
+    detail::check(b200_peer_allreduce_sum_f64(_ar_ctx, d_val, n, gpu->get_cuda_stream()), "peer allreduce");
+  else
+    detail::check(b200_allreduce_sum_f64(gpu->nccl_comm(), d_val, n, gpu->get_cuda_stream()), "nccl allreduce");
+}
+void L2GMap::teardown_peer_reduce()
+{
+  b200_peer_reduce_destroy(_ar_ctx);
+  _ar_ctx = nullptr;
+  for (size_t q = 0; q < _ar_boxes.size(); ++q)
+    if (_ar_boxes[q] && static_cast<int>(q) != _mpi_rank)
+      b200_ipc_close(_ar_boxes[q]);
+  _ar_boxes.clear();
+  if (_ar_box)
+    b200_free(_ar_box);
+  _ar_box = nullptr;
 }
 //-----------------------------------------------------------------------------
 template <typename T>
@@ -241,6 +308,7 @@ L2GMap::~L2GMap()
     b200_ipc_close(p);
   if (_stage)
     b200_free(_stage);
+  teardown_peer_reduce();
 }
 //-----------------------------------------------------------------------------
 template <typename T>

@@ -196,6 +196,10 @@ int spmvh_l2g_reverse_update_f64(void* map, double* d_vec)
 {
   return guarded([&] { as_map(map).reverse_update(d_vec); });
 }
+int spmvh_l2g_allreduce_f64(void* map, double* d_val, int32_t n, int use_nccl)
+{
+  return guarded([&] { as_map(map).allreduce_sum(d_val, n, use_nccl != 0); });
+}
 
 int spmvh_matrix_create(void** mat, void* exec, const int32_t* rowptr, const int32_t* colind, const double* values,
                         int64_t nrows_local, int64_t ncols_local, const int64_t* row_ghosts, int64_t num_row_ghosts,

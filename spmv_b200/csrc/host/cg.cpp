@@ -56,6 +56,14 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   detail::check(b200_set_device(exec.get_device_id()), "cudaSetDevice");
   void* stream = exec.get_cuda_stream();
   void* nccl = exec.nccl_comm();
+  // scalar sums: one small kernel over peer memory when the column map set it up, else NCCL
+  void* peer = col_l2g->peer_reduce();
+  auto allreduce = [&](double* d_val) {
+    if (peer)
+      detail::check(b200_peer_allreduce_sum_f64(peer, d_val, 1, stream), "cg allreduce (peer)");
+    else
+      detail::check(b200_allreduce_sum_f64(nccl, d_val, 1, stream), "cg allreduce");
+  };
 
   const int M = row_l2g->local_size();
   const int N_padded = col_l2g->local_size() + col_l2g->num_ghosts();
@@ -102,7 +110,7 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
 
     // rnorm0 = sqrt(allreduce(r.r))  (cg.cpp:47-50)
     detail::check(b200_cg_dot_f64(M, r, r, state + 2, scratch, nullptr, stream), "cg dot");
-    detail::check(b200_allreduce_sum_f64(nccl, state + 2, 1, stream), "cg allreduce");
+    allreduce(state + 2);
     detail::check(b200_cg_init_state(state, state + 2, rtol, kmax, stream), "cg init");
 
     // fused p.Ap epilogue: single general block only
@@ -129,9 +137,9 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
         A.mult(p, Ap);
         detail::check(b200_cg_dot_f64(M, p, Ap, state + 1, scratch, state + 4, stream), "cg dot");
       }
-      detail::check(b200_allreduce_sum_f64(nccl, state + 1, 1, stream), "cg allreduce"); // cg.cpp:65
+      allreduce(state + 1); // cg.cpp:65
       detail::check(b200_cg_update_xr_f64(M, state, p, Ap, x_padded, r, stream), "cg update x,r");
-      detail::check(b200_allreduce_sum_f64(nccl, state + 2, 1, stream), "cg allreduce"); // cg.cpp:75
+      allreduce(state + 2); // cg.cpp:75
       detail::check(b200_cg_update_p_f64(M, state, r, p, hist, hist_len, stream), "cg update p");
       detail::check(b200_memcpy_d2h_async(&h_flags[slot], state + 4, sizeof(Flags), stream), "flag copy");
       detail::check(b200_event_record(events[slot], stream), "event record");

@@ -16,6 +16,8 @@
 // plain-loop restatement of daxpy/dscal.
 #include "common.cuh"
 
+#include <cstring>
+
 #include <algorithm>
 
 namespace b200
@@ -167,6 +169,73 @@ static int need_gpu()
 
 using namespace b200;
 
+
+// ---------------------------------------------------------------------------
+// Scalar allreduce over peer memory (the MPI_Allreduce of cg.cpp:49,65,75 on device
+// scalars).  Every rank owns a mailbox in IPC-exported device memory: one slot per
+// (parity, source rank).  One warp per rank: lane q stores this rank's values and then
+// the sequence number (release, system scope) into rank q's mailbox over NVLink; lane q
+// then spins (acquire) on the slot rank q writes here.  The sum runs over the ranks in
+// rank order on every rank, so all ranks get the same bits.  Two parities: a rank can
+// only be one allreduce ahead of the slowest one (it needs that rank's current value
+// to finish), so the slot it overwrites has been consumed.
+// ---------------------------------------------------------------------------
+struct PeerSlot {
+  double v[B200_PEER_REDUCE_MAX_COUNT];
+  unsigned long long seq;
+  unsigned long long pad[3];
+};
+static_assert(sizeof(PeerSlot) == 64, "one slot per 64-byte line");
+
+struct PeerDesc {
+  int rank, world;
+  unsigned long long seq;
+  PeerSlot* box[B200_PEER_REDUCE_MAX_RANKS]; // box[q] = rank q's mailbox (box[rank]: mine, local)
+};
+
+__global__ void __launch_bounds__(32) peer_allreduce_kernel(PeerDesc* d, double* val, int count)
+{
+  const int lane = threadIdx.x;
+  const int rank = d->rank, world = d->world;
+  const unsigned long long seq = d->seq + 1;
+  const int par = (int)(seq & 1ull);
+  __syncwarp();
+  double mine[B200_PEER_REDUCE_MAX_COUNT], got[B200_PEER_REDUCE_MAX_COUNT];
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
+    mine[k] = k < count ? val[k] : 0.0;
+    got[k] = 0.0;
+  }
+  if (lane < world) {
+    PeerSlot* dst = d->box[lane] + par * world + rank;
+#pragma unroll
+    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+      if (k < count)
+        asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&dst->v[k]), "d"(mine[k]) : "memory");
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->seq), "l"(seq) : "memory");
+    const PeerSlot* src = d->box[rank] + par * world + lane;
+    unsigned long long seen;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->seq) : "memory");
+    } while (seen != seq);
+#pragma unroll
+    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+      if (k < count)
+        asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(got[k]) : "l"(&src->v[k]) : "memory");
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
+    double total = 0.0;
+    for (int q = 0; q < world; ++q)
+      total = add_rn(total, __shfl_sync(0xffffffffu, got[k], q));
+    if (lane == 0 && k < count)
+      val[k] = total;
+  }
+  if (lane == 0)
+    d->seq = seq;
+}
+
 extern "C" {
 
 int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, double* d_out,
@@ -220,6 +289,63 @@ int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* 
     return rc;
   update_p_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_r, d_p, d_hist,
                                                                       hist_len);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_peer_reduce_mailbox_bytes(int32_t world, size_t* num_bytes)
+{
+  B200_REQUIRE(num_bytes != nullptr && world >= 1 && world <= B200_PEER_REDUCE_MAX_RANKS, "bad argument");
+  *num_bytes = sizeof(PeerSlot) * 2 * (size_t)world;
+  return B200_OK;
+}
+
+int b200_peer_reduce_create(void** ctx, int32_t rank, int32_t world, void* const* d_mailboxes, void* stream)
+{
+  B200_REQUIRE(ctx != nullptr && d_mailboxes != nullptr, "bad argument");
+  *ctx = nullptr;
+  B200_REQUIRE(world >= 1 && world <= B200_PEER_REDUCE_MAX_RANKS && rank >= 0 && rank < world, "bad rank / world");
+  if (int rc = need_gpu())
+    return rc;
+  PeerDesc h;
+  std::memset(&h, 0, sizeof(h));
+  h.rank = rank;
+  h.world = world;
+  for (int q = 0; q < world; ++q) {
+    B200_REQUIRE(d_mailboxes[q] != nullptr, "mailbox is NULL");
+    h.box[q] = static_cast<PeerSlot*>(d_mailboxes[q]);
+  }
+  PeerDesc* d = nullptr;
+  B200_CUDA(cudaMalloc(&d, sizeof(PeerDesc)));
+  cudaStream_t st = as_stream(stream);
+  // my mailbox starts at sequence 0 everywhere; peers zero theirs the same way before anyone reduces
+  // (the caller puts a barrier between create and the first allreduce)
+  if (cudaMemsetAsync(h.box[rank], 0, sizeof(PeerSlot) * 2 * (size_t)world, st) != cudaSuccess
+      || cudaMemcpyAsync(d, &h, sizeof(h), cudaMemcpyHostToDevice, st) != cudaSuccess
+      || cudaStreamSynchronize(st) != cudaSuccess) {
+    cudaFree(d);
+    return cuda_fail(cudaGetLastError(), "peer_reduce_create", __FILE__, __LINE__);
+  }
+  *ctx = d;
+  return B200_OK;
+}
+
+int b200_peer_reduce_destroy(void* ctx)
+{
+  if (ctx)
+    B200_CUDA(cudaFree(ctx));
+  return B200_OK;
+}
+
+int b200_peer_allreduce_sum_f64(void* ctx, double* d_inout, int32_t n, void* stream)
+{
+  B200_REQUIRE(n >= 0 && n <= B200_PEER_REDUCE_MAX_COUNT, "count out of range");
+  if (n == 0 || ctx == nullptr) // single rank: the local value is the sum
+    return B200_OK;
+  B200_REQUIRE(d_inout != nullptr, "NULL value");
+  if (int rc = need_gpu())
+    return rc;
+  peer_allreduce_kernel<<<1, 32, 0, as_stream(stream)>>>(static_cast<PeerDesc*>(ctx), d_inout, n);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -188,6 +188,26 @@ def main():
                 A0.close()
                 A1.close()
 
+    # scalar allreduce of the CG loop: peer-memory kernel (when the ranks can map each other) and NCCL
+    # give the same bits on every rank, repeatedly (the mailboxes are double-buffered by parity)
+    if mode == "gpu":
+        A = api.create_laplace3d(ex, 6, 5, 8 * size, 7, False, api.P2P_NONBLOCKING)
+        cmap = A.col_map()
+        for use_nccl in (False, True):
+            for rep in range(5):
+                v = torch.tensor([rank + 1.0, 0.25 * (rank + rep), -1e-3 * rank], dtype=torch.float64, device=dev)
+                cmap.allreduce_sum(v, nccl=use_nccl)
+                ex.synchronize()
+                want = [sum(r + 1.0 for r in range(size)), sum(0.25 * (r + rep) for r in range(size)),
+                        sum(-1e-3 * r for r in range(size))]
+                got = v.cpu().numpy()
+                check(np.allclose(got, want, rtol=1e-15, atol=0) and got[0] == want[0],
+                      f"allreduce_sum nccl={use_nccl} rep={rep} size={size}: {got} vs {want}")
+                gathered = [torch.zeros_like(v) for _ in range(size)]
+                dist.all_gather(gathered, v)
+                check(all(torch.equal(g, gathered[0]) for g in gathered), f"allreduce_sum nccl={use_nccl}: ranks disagree")
+        A.close()
+
     # mult_host on slabs big enough for several chunks and distinct edge pages
     if mode == "gpu":
         for st, sym, cm in ((7, True, api.P2P_NONBLOCKING), (27, False, api.P2P_NONBLOCKING),
