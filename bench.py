@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 NX = NY = 256
 NZ_PER_GPU = 256
 CPU_SAMPLE_NZ = 64  # planes of the CPU legs' slab (1/4 of the 1-GPU workload)
+CONFIG5_ROWS_PER_GPU = 6_250_000  # BASELINE configs[4]: ~50 M rows on 8 GPUs
 
 
 def parse():
@@ -37,6 +38,8 @@ def parse():
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling (BASELINE configs[2]): the 256^3 grid split over the GPUs, nz = 256 / N")
     ap.add_argument("--no-extras", action="store_true", help="skip the 'also' measurements and cpu_baseline")
+    ap.add_argument("--config5-rows", type=int, default=CONFIG5_ROWS_PER_GPU,
+                    help="rows per GPU of the power-law / PETSc leg (default 6.25 M = 50 M rows at 8 GPUs; 0 skips it)")
     return ap.parse_args()
 
 
@@ -122,14 +125,14 @@ def bytes_symmetric(nnz_lower, nnz_remote, rows, nghosts):
 class Operator:
     """One rank's spmv::Matrix of the slab-partitioned Laplacian plus its vectors."""
 
-    def __init__(self, api, ex, dev, rank, size, nz, stencil, symmetric):
+    def __init__(self, api, ex, dev, rank, size, nz, stencil, symmetric, matrix=None, row0=None, n_glob=None):
         import torch
         from spmv_b200 import synth
         self.api, self.ex, self.torch = api, ex, torch
         self.symmetric, self.stencil, self.size = symmetric, stencil, size
         # overlap schedule (local block while the halo is in flight) whenever there are neighbours
         cm = api.P2P_NONBLOCKING if size > 1 else api.P2P_BLOCKING
-        self.A = api.create_laplace3d(ex, NX, NY, nz * size, stencil, symmetric, cm)
+        self.A = matrix if matrix is not None else api.create_laplace3d(ex, NX, NY, nz * size, stencil, symmetric, cm)
         info = self.A._info()
         self.rows, self.nnz_local, self.nnz_remote = info[0], info[6], info[7]
         self.two_blocks = bool(info[5])
@@ -137,9 +140,10 @@ class Operator:
         self.nghosts = self.col_map.num_ghosts()
         self.ncols = self.rows + self.nghosts
         self.nnbr = len(self.col_map.get("neighbours")) if size > 1 else 0
-        n_glob = self.rows * size
+        n_glob = self.rows * size if n_glob is None else n_glob
+        row0 = rank * self.rows if row0 is None else row0
         self.x = torch.zeros(self.ncols, dtype=torch.float64, device=dev)
-        self.x[: self.rows] = torch.from_numpy(synth.bump_vector(n_glob, rank * self.rows, (rank + 1) * self.rows)).to(dev)
+        self.x[: self.rows] = torch.from_numpy(synth.bump_vector(n_glob, row0, row0 + self.rows)).to(dev)
         self.y = torch.empty(self.rows, dtype=torch.float64, device=dev)
         # our kernels per step: pack (if neighbours) + local block + remote block (if it has entries)
         self.launches_per_step = (1 if self.nnbr else 0) + 1 + (1 if self.nnz_remote > 0 else 0)
@@ -241,6 +245,77 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
             raise RuntimeError(f"mult_host disagrees with update+mult: rel max err {err}")
         out["e2e"] = {"value": op.algorithmic_bytes() * op.size / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s",
                       "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M}
+    return out
+
+
+def measure_config5(api, ex, dev, rank, size, timer, peak, rows_per_gpu):
+    """BASELINE configs[4]: irregular power-law rows, written as a PETSc binary file by the host-core
+    generator (demos/CreatePowerLaw.h), read back with read_petsc_binary_matrix, general CSR SpMV
+    (update + mult).  6.25 M rows per GPU: the 50 M-row matrix at 8 GPUs."""
+    import numpy as np
+    import shutil
+    import tempfile
+    import torch
+    from spmv_b200 import synth
+    n = rows_per_gpu * size
+    root = "/dev/shm" if os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > 110 * n + (1 << 30) \
+        else tempfile.gettempdir()
+    path = os.path.join(root, f"spmv_b200_config5_{os.environ.get('MASTER_PORT', str(os.getpid()))}.petsc")
+    t_gen = nnz_glob = file_bytes = None
+    if rank == 0:
+        t0 = time.perf_counter()
+        nnz_glob = api.write_powerlaw_petsc(path, n)
+        t_gen = time.perf_counter() - t0
+    if size > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    try:
+        t0 = time.perf_counter()
+        cm = api.P2P_NONBLOCKING if size > 1 else api.P2P_BLOCKING
+        A = api.read_petsc_binary_matrix(path, ex, False, cm)
+        torch.cuda.synchronize()
+        t_read = time.perf_counter() - t0
+        if size > 1:
+            import torch.distributed as dist
+            dist.barrier()
+    finally:
+        if rank == 0 and os.path.exists(path):
+            file_bytes = os.path.getsize(path)
+            os.remove(path)
+    r0 = int(synth.owner_ranges(size, n)[rank])
+    op = Operator(api, ex, dev, rank, size, 0, 0, False, matrix=A, row0=r0, n_glob=n)
+    m = measure_spmv(op, timer, 30, 5, peak, with_e2e=False)
+    # parity at full size: any rank can regenerate any row, and x is a formula of the global index --
+    # recompute a sample of this rank's rows on the host (left-to-right sums, csr_kernels.cpp:42-49)
+    rng = np.random.default_rng(20261104 + rank)
+    y = op.y.cpu().numpy()
+    worst = 0.0
+    picks = np.unique(np.concatenate([rng.integers(0, op.rows, 256), [0, op.rows - 1]]))
+    for lr in picks:
+        rp, col, val = api.powerlaw_rows(n, r0 + int(lr), r0 + int(lr) + 1)
+        xs = np.exp(-10.0 * np.power(5.0 * (col.astype(np.float64) / float(n) - 0.5), 2.0))
+        want = 0.0
+        for v, xv in zip(val, xs):
+            want += v * xv
+        worst = max(worst, abs(want - y[lr]) / max(abs(want), 1e-300))
+    if not worst <= 1e-12:
+        raise RuntimeError(f"config 5: y differs from the regenerated rows, rel err {worst}")
+    t = torch.tensor([float(op.nghosts), float(op.nnbr), worst, t_read], dtype=torch.float64, device=dev)
+    if size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out = {"rows_global": n, "rows_per_gpu": op.rows, "nnz_global": nnz_glob, "GBps": m["GBps"], "GFLOPs": m["GFLOPs"],
+           "ms_per_step": m["ms_per_step"], "local_kernel_ms_avg": m["kernel_ms_avg"],
+           "local_kernel_GBps": m["kernel_GBps"], "local_kernel_frac_of_hbm_peak": m["frac_of_hbm_peak"],
+           "algorithmic_bytes_rank0": op.algorithmic_bytes(), "max_ghosts_per_rank": int(t[0].item()),
+           "max_neighbours": int(t[1].item()), "halo_bytes_in_per_rank_max": 8 * int(t[0].item()),
+           "generate_and_write_s": t_gen, "read_petsc_s_max": float(t[3].item()),
+           "file_bytes": file_bytes if rank == 0 else None,
+           "parity": {"rows_checked_per_rank": int(len(picks)), "max_rel_err": float(t[2].item()),
+                      "how": "sampled rows regenerated on the host, sequential fp64 row sums, tolerance 1e-12"},
+           "input": "synth.powerlaw_rows definition: Pareto(2, 4) row lengths clamped to [1, 4096], 90 % of the "
+                    "columns in a +-32768 band, 10 % anywhere; PETSc binary file -> read_petsc_binary_matrix"}
+    op.close()
     return out
 
 
@@ -375,6 +450,9 @@ def run_b200(args):
         also["cg_sym_7pt"] = measure_cg(api, ops, timer, dev, size)
         ops.close()
         del ops
+        # ---- config 5: power-law rows through the PETSc reader --------------------------
+        if args.config5_rows > 0:
+            also["powerlaw_petsc"] = measure_config5(api, ex, dev, rank, size, timer, peak, args.config5_rows)
 
     if rank != 0:
         return

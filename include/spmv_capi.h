@@ -95,6 +95,18 @@ SPMVH_API int spmvh_write_petsc_matrix(const char* filename, int32_t nrows, int3
 SPMVH_API int spmvh_write_petsc_vector(const char* filename, int32_t n, const double* values);
 SPMVH_API int spmvh_read_petsc_vector(void* exec, const char* filename, double** d_vec, int64_t* n_local);
 
+/* ---- config-5 input: power-law rows (demos/CreatePowerLaw.h), host cores only ----
+ * counts: entries per row for rows [r0, r1); fill: the rows in CSR order at rowstart[]
+ * (exclusive prefix sums of counts, r1 - r0 + 1 long), global column ids;
+ * write: the whole n x n matrix as a PETSc binary file for spmvh_matrix_read_petsc. */
+SPMVH_API int spmvh_powerlaw_counts(int64_t n, uint64_t seed, double alpha, double xmin, int64_t max_len,
+                                    int64_t band, double p_global, int64_t r0, int64_t r1, int32_t* counts);
+SPMVH_API int spmvh_powerlaw_fill(int64_t n, uint64_t seed, double alpha, double xmin, int64_t max_len, int64_t band,
+                                  double p_global, int64_t r0, int64_t r1, const int64_t* rowstart, int64_t* col,
+                                  double* val);
+SPMVH_API int spmvh_write_powerlaw_petsc(const char* filename, int64_t n, uint64_t seed, double alpha, double xmin,
+                                         int64_t max_len, int64_t band, double p_global, int64_t* nnz);
+
 #ifdef __cplusplus
 }
 #endif

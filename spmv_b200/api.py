@@ -65,6 +65,9 @@ _SIG = {
     "spmvh_write_petsc_matrix": [C.c_char_p, _i32, _i32, _p, _p, _p],
     "spmvh_write_petsc_vector": [C.c_char_p, _i32, _p],
     "spmvh_read_petsc_vector": [_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(_i64)],
+    "spmvh_powerlaw_counts": [_i64, C.c_uint64, _f64, _f64, _i64, _i64, _f64, _i64, _i64, _p],
+    "spmvh_powerlaw_fill": [_i64, C.c_uint64, _f64, _f64, _i64, _i64, _f64, _i64, _i64, _p, _p, _p],
+    "spmvh_write_powerlaw_petsc": [C.c_char_p, _i64, C.c_uint64, _f64, _f64, _i64, _i64, _f64, C.POINTER(_i64)],
     "spmv_shim_run_ranks": [_int, RANK_FN, _p],
     "spmv_shim_set_world_callbacks": [_int, _int, BARRIER_FN, ALLTOALLV_FN, _p],
 }
@@ -484,6 +487,29 @@ def write_petsc_binary_matrix(filename, nrows, ncols, rowptr, colind, values):
 def write_petsc_binary_vector(filename, values):
     v = np.ascontiguousarray(values, dtype=np.float64)
     _ck(host_lib().spmvh_write_petsc_vector(os.fsencode(filename), len(v), _np_ptr(v)))
+
+
+def powerlaw_rows(n, r0, r1, seed=20261104, alpha=2.0, xmin=4.0, max_len=4096, band=32768, p_global=0.1):
+    """demos/CreatePowerLaw.h: rows [r0, r1) of the config-5 matrix from the host-core generator
+    (same definition and defaults as synth.powerlaw_rows) -> (rowptr int64, global cols int64, values)."""
+    spec = (int(n), int(seed), float(alpha), float(xmin), int(max_len), int(band), float(p_global))
+    counts = np.zeros(max(r1 - r0, 1), np.int32)
+    _ck(host_lib().spmvh_powerlaw_counts(*spec, int(r0), int(r1), _np_ptr(counts)))
+    rowptr = np.zeros(r1 - r0 + 1, np.int64)
+    np.cumsum(counts[:r1 - r0], out=rowptr[1:])
+    col = np.zeros(max(int(rowptr[-1]), 1), np.int64)
+    val = np.zeros(max(int(rowptr[-1]), 1), np.float64)
+    _ck(host_lib().spmvh_powerlaw_fill(*spec, int(r0), int(r1), _np_ptr(rowptr), _np_ptr(col), _np_ptr(val)))
+    return rowptr, col[:rowptr[-1]], val[:rowptr[-1]]
+
+
+def write_powerlaw_petsc(filename, n, seed=20261104, alpha=2.0, xmin=4.0, max_len=4096, band=32768, p_global=0.1):
+    """The whole n x n config-5 matrix as a PETSc binary file (input of read_petsc_binary_matrix);
+    returns the entry count."""
+    nnz = _i64()
+    _ck(host_lib().spmvh_write_powerlaw_petsc(os.fsencode(filename), int(n), int(seed), float(alpha), float(xmin),
+                                              int(max_len), int(band), float(p_global), C.byref(nnz)))
+    return nnz.value
 
 
 def create_A(N, exec):

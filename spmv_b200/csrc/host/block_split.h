@@ -72,12 +72,12 @@ inline std::int32_t canonicalise_row(std::int32_t* col, T* val, std::int32_t len
 }
 
 template <typename T>
-inline void canonicalise(HostCSR<T>& m)
+inline void canonicalise(HostCSR<T>& m, int nthreads = 1)
 {
   const std::int32_t n = m.rows;
   std::vector<std::int32_t> newlen(n);
   bool shrunk = false;
-#pragma omp parallel
+#pragma omp parallel num_threads(nthreads)
   {
     std::vector<std::int32_t> perm, ctmp;
     std::vector<T> vtmp;

@@ -3,6 +3,7 @@
 
 #include "../../../demos/CreateA.h"
 #include "../../../demos/CreateLaplace3D.h"
+#include "../../../demos/CreatePowerLaw.h"
 #include "host_util.h"
 #include <spmv/spmv.h>
 
@@ -355,6 +356,37 @@ int spmvh_read_petsc_vector(void* exec, const char* filename, double** d_vec, in
     const std::int64_t n = (std::int64_t(h[4]) << 24) | (std::int64_t(h[5]) << 16) | (std::int64_t(h[6]) << 8) | h[7];
     const auto ranges = detail::owner_ranges(size, n);
     *n_local = ranges[rank + 1] - ranges[rank];
+  });
+}
+
+namespace
+{
+PowerLawSpec as_spec(int64_t n, uint64_t seed, double alpha, double xmin, int64_t max_len, int64_t band, double p_global)
+{
+  PowerLawSpec s;
+  s.n = n, s.seed = seed, s.alpha = alpha, s.xmin = xmin, s.max_len = max_len, s.band = band, s.p_global = p_global;
+  return s;
+}
+} // namespace
+
+int spmvh_powerlaw_counts(int64_t n, uint64_t seed, double alpha, double xmin, int64_t max_len, int64_t band,
+                          double p_global, int64_t r0, int64_t r1, int32_t* counts)
+{
+  return guarded([&] { powerlaw_row_counts(as_spec(n, seed, alpha, xmin, max_len, band, p_global), r0, r1, counts); });
+}
+int spmvh_powerlaw_fill(int64_t n, uint64_t seed, double alpha, double xmin, int64_t max_len, int64_t band,
+                        double p_global, int64_t r0, int64_t r1, const int64_t* rowstart, int64_t* col, double* val)
+{
+  return guarded(
+      [&] { powerlaw_rows_fill(as_spec(n, seed, alpha, xmin, max_len, band, p_global), r0, r1, rowstart, col, val); });
+}
+int spmvh_write_powerlaw_petsc(const char* filename, int64_t n, uint64_t seed, double alpha, double xmin,
+                               int64_t max_len, int64_t band, double p_global, int64_t* nnz)
+{
+  return guarded([&] {
+    const std::int64_t m = write_powerlaw_petsc(filename, as_spec(n, seed, alpha, xmin, max_len, band, p_global));
+    if (nnz)
+      *nnz = m;
   });
 }
 

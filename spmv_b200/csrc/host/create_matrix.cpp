@@ -12,6 +12,7 @@
 #include "L2GMap.h"
 #include "block_split.h"
 #include "device_executor.h"
+#include "host_util.h"
 
 #include <algorithm>
 #include <numeric>
@@ -183,12 +184,15 @@ Matrix<T>* Matrix<T>::create_matrix(MPI_Comm comm, std::shared_ptr<DeviceExecuto
     blocks[LOCAL].cols = static_cast<std::int32_t>(ncols_local);
   std::vector<T> diagonal;
   std::vector<char> has_diag;
+  int mpi_size_for_threads = 1;
+  MPI_Comm_size(comm, &mpi_size_for_threads);
+  const int nthreads = detail::host_threads(mpi_size_for_threads);
   if (symmetric) {
     diagonal.assign(n, T(0));
     has_diag.assign(n, 0);
   }
 
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(nthreads)
   for (std::int32_t r = 0; r < n; ++r) {
     std::int32_t cnt[2] = {0, 0};
     for (std::int32_t j = rowptr[r]; j < rowptr[r + 1]; ++j) {
@@ -220,7 +224,7 @@ Matrix<T>* Matrix<T>::create_matrix(MPI_Comm comm, std::shared_ptr<DeviceExecuto
     filled[LOCAL].assign(n, 0);
     filled[REMOTE].assign(n, 0);
   }
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(nthreads)
   for (std::int32_t r = 0; r < n; ++r) {
     std::int32_t w[2] = {blocks[LOCAL].rowptr[r], blocks[REMOTE].rowptr[r]};
     for (std::int32_t j = rowptr[r]; j < rowptr[r + 1]; ++j) {
@@ -251,8 +255,8 @@ Matrix<T>* Matrix<T>::create_matrix(MPI_Comm comm, std::shared_ptr<DeviceExecuto
       has_diag[e.row] = 1;
     }
   }
-  canonicalise(blocks[LOCAL]);
-  canonicalise(blocks[REMOTE]);
+  canonicalise(blocks[LOCAL], nthreads);
+  canonicalise(blocks[REMOTE], nthreads);
 
   // ---- maps and the Matrix (Matrix.cpp:410-479) ------------------------------
   auto col_map = std::make_shared<spmv::L2GMap>(comm, ncols_local, new_col_ghosts, exec, cm);

@@ -4,6 +4,8 @@
 #include "b200spmv.h"
 
 #include <cstdint>
+#include <cstdlib>
+#include <sched.h>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -29,6 +31,25 @@ inline std::vector<std::int64_t> owner_ranges(int size, std::int64_t N)
   for (int rank = 0; rank <= size; ++rank)
     ranges[rank] = rank < r ? rank * (n + 1) : rank * n + r;
   return ranges;
+}
+
+/// Threads for the host-side builders: SPMV_HOST_THREADS if set, else the CPUs this process may run
+/// on divided by `sharers` (ranks doing the same work at the same time).  Launchers such as torchrun
+/// export OMP_NUM_THREADS=1, which would serialise a 50 M-row setup; the builders pass this count to
+/// their parallel regions explicitly instead of relying on the OpenMP default.
+inline int host_threads(int sharers = 1)
+{
+  if (const char* e = std::getenv("SPMV_HOST_THREADS"))
+    if (std::atoi(e) > 0)
+      return std::atoi(e);
+  cpu_set_t set;
+  CPU_ZERO(&set);
+  int n = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : 1;
+  if (const char* e = std::getenv("LOCAL_WORLD_SIZE"))
+    if (std::atoi(e) > 0)
+      sharers = std::atoi(e);
+  n /= sharers > 0 ? sharers : 1;
+  return n > 0 ? n : 1;
 }
 
 } // namespace detail

@@ -35,10 +35,12 @@ void read_exact(std::ifstream& f, void* dst, std::size_t bytes)
     throw std::runtime_error("Unexpected end of PETSc file");
 }
 
+int g_threads = 1; // set per call from detail::host_threads
+
 void read_i32_be(std::ifstream& f, std::int32_t* dst, std::size_t n)
 {
   read_exact(f, dst, n * 4);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(g_threads)
   for (std::size_t i = 0; i < n; ++i) {
     std::uint32_t u;
     std::memcpy(&u, dst + i, 4);
@@ -50,7 +52,7 @@ void read_i32_be(std::ifstream& f, std::int32_t* dst, std::size_t n)
 void read_f64_be(std::ifstream& f, double* dst, std::size_t n)
 {
   read_exact(f, dst, n * 8);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(g_threads)
   for (std::size_t i = 0; i < n; ++i) {
     std::uint64_t u;
     std::memcpy(&u, dst + i, 8);
@@ -73,6 +75,7 @@ Matrix<double> read_petsc_binary_matrix(std::string filename, MPI_Comm comm, std
   int mpi_rank = 0, mpi_size = 1;
   CHECK_MPI(MPI_Comm_rank(comm, &mpi_rank));
   CHECK_MPI(MPI_Comm_size(comm, &mpi_size));
+  g_threads = host_threads(mpi_size);
 
   std::ifstream file(filename.c_str(), std::ios::in | std::ios::binary);
   if (!file.is_open())
@@ -139,7 +142,7 @@ Matrix<double> read_petsc_binary_matrix(std::string filename, MPI_Comm comm, std
   }
   std::vector<double> diagonal(symmetric ? n : 0, 0.0);
   std::vector<std::int32_t> lcol(nnz_size);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(g_threads)
   for (std::int32_t r = 0; r < n; ++r) {
     std::int32_t cnt[2] = {0, 0};
     for (std::int64_t j = rowstart[r]; j < rowstart[r + 1]; ++j) {
@@ -161,7 +164,7 @@ Matrix<double> read_petsc_binary_matrix(std::string filename, MPI_Comm comm, std
     b.colind.resize(b.rowptr[n]);
     b.values.resize(b.rowptr[n]);
   }
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(g_threads)
   for (std::int32_t r = 0; r < n; ++r) {
     std::int32_t w[2] = {blocks[LOCAL].rowptr[r], blocks[REMOTE].rowptr[r]};
     for (std::int64_t j = rowstart[r]; j < rowstart[r + 1]; ++j) {
@@ -175,8 +178,8 @@ Matrix<double> read_petsc_binary_matrix(std::string filename, MPI_Comm comm, std
       }
     }
   }
-  canonicalise(blocks[LOCAL]); // rows ordered by local column id, like insert + makeCompressed
-  canonicalise(blocks[REMOTE]);
+  canonicalise(blocks[LOCAL], g_threads); // rows ordered by local column id, like insert + makeCompressed
+  canonicalise(blocks[REMOTE], g_threads);
 
   auto col_map = std::make_shared<spmv::L2GMap>(comm, ncols_local, ghosts, exec, cm);
   auto row_map = std::make_shared<spmv::L2GMap>(comm, nrows_local, std::vector<std::int64_t>(), exec, cm);

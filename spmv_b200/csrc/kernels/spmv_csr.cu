@@ -746,23 +746,44 @@ __global__ void spmv_rowlist_kernel(int n, const int32_t* __restrict__ rowlist,
   y[r] = add_rn(mul_rn(alpha, sum), mul_rn(beta, y[r]));
 }
 
+// Mixed row lengths (the remote block of an irregular matrix: a mean of 1-2 entries per listed
+// row, a few rows of hundreds): lanes = consecutive listed rows as above; rows longer than
+// SHORT_ROW are handed to the whole warp one after the other (lane-strided + xor-tree).  One
+// warp per row for every row cost 430 us on config 5's remote block at 2 GPUs (1.8 M listed
+// rows, 1.3 entries each: three dependent round trips per warp for one product).
 template <typename T>
-__global__ void spmv_rowlist_warp_kernel(int n, const int32_t* __restrict__ rowlist,
-                                         const int32_t* __restrict__ rowptr,
-                                         const int32_t* __restrict__ colind, const T* __restrict__ val,
-                                         const T* __restrict__ x, T alpha, T beta, T* __restrict__ y)
+__global__ void spmv_rowlist_mixed_kernel(int n, const int32_t* __restrict__ rowlist,
+                                          const int32_t* __restrict__ rowptr,
+                                          const int32_t* __restrict__ colind, const T* __restrict__ val,
+                                          const T* __restrict__ x, T alpha, T beta, T* __restrict__ y)
 {
-  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (k >= n)
-    return;
-  const int r = __ldg(rowlist + k);
-  const int rs = __ldg(rowptr + r), re = __ldg(rowptr + r + 1);
-  T part = 0;
-  for (int j = rs + lane; j < re; j += 32)
-    part = fma(__ldg(val + j), __ldg(x + __ldg(colind + j)), part);
-  part = warp_sum(part);
-  if (lane == 0)
-    y[r] = add_rn(mul_rn(alpha, part), mul_rn(beta, y[r]));
+  constexpr unsigned FULL = 0xffffffffu;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+  int r = 0, rs = 0, re = 0;
+  if (k < n) {
+    r = __ldg(rowlist + k);
+    rs = __ldg(rowptr + r);
+    re = __ldg(rowptr + r + 1);
+  }
+  const bool is_long = re - rs > SHORT_ROW;
+  if (k < n && !is_long) {
+    T sum = 0;
+    for (int j = rs; j < re; ++j)
+      sum = add_rn(sum, mul_rn(__ldg(val + j), __ldg(x + __ldg(colind + j))));
+    y[r] = add_rn(mul_rn(alpha, sum), mul_rn(beta, y[r]));
+  }
+  unsigned todo = __ballot_sync(FULL, is_long);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const int qs = __shfl_sync(FULL, rs, src), qe = __shfl_sync(FULL, re, src), qr = __shfl_sync(FULL, r, src);
+    T part = 0;
+    for (int j = qs + lane; j < qe; j += 32)
+      part = fma(__ldg(val + j), __ldg(x + __ldg(colind + j)), part);
+    part = warp_sum(part);
+    if (lane == 0)
+      y[qr] = add_rn(mul_rn(alpha, part), mul_rn(beta, y[qr]));
+  }
 }
 
 struct RowNonEmpty {
@@ -1165,8 +1186,8 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
       spmv_rowlist_kernel<T><<<(n + 127) / 128, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
                                                               alpha, beta, d_y);
     else
-      spmv_rowlist_warp_kernel<T><<<(n + 7) / 8, 256, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
-                                                               alpha, beta, d_y);
+      spmv_rowlist_mixed_kernel<T><<<(n + 127) / 128, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x,
+                                                                    alpha, beta, d_y);
     B200_LAUNCH_CHECK();
     return B200_OK;
   }

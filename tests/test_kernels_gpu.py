@@ -173,8 +173,8 @@ def test_sparse_row_block(cuda, long_rows, alpha, beta):
     assert rel_l2(y, want) < TOL
     if beta == 1.0:
         assert np.array_equal(y[lens == 0], y0[lens == 0])
-        if not long_rows:
-            assert np.array_equal(y, want)  # one thread per row, reference order
+        short = lens <= 32
+        assert np.array_equal(y[short], want[short])  # one thread per row, reference order
 
 
 def test_zero_rows_and_zero_nnz(cuda):

@@ -179,3 +179,32 @@ def test_restated_cg_equals_reference(kind, n):
                 assert np.array_equal(x, x_ref)
             else:
                 assert np.linalg.norm(x - x_ref) <= 1e-14 * np.linalg.norm(x_ref)
+
+
+# ---- config-5 input: the host-core power-law generator (demos/CreatePowerLaw.h) ----
+@pytest.mark.parametrize("n,band", [(1, 8), (2, 8), (3000, 187), (60000, 32768)])
+def test_powerlaw_generator_equals_numpy_definition(n, band):
+    from spmv_b200 import api, synth
+    want = synth.powerlaw_rows(n, 0, n, band=band)
+    got = api.powerlaw_rows(n, 0, n, band=band)
+    for a, b in zip(want, got):
+        assert np.array_equal(a, b)
+    if n > 10:  # any rank can generate any row range
+        r0, r1 = n // 3, n // 2
+        for a, b in zip(synth.powerlaw_rows(n, r0, r1, band=band), api.powerlaw_rows(n, r0, r1, band=band)):
+            assert np.array_equal(a, b)
+
+
+def test_powerlaw_petsc_file_is_the_same_bytes(tmp_path):
+    """The streamed writer (chunks written out of order at their offsets) against the plain
+    writer fed with the numpy rows: same file, byte for byte (format: SURVEY.md Appendix E)."""
+    from spmv_b200 import api, synth
+    n = 150000  # > 2 chunks of 65536 rows
+    rp, col, val = synth.powerlaw_rows(n, 0, n)
+    a, b = str(tmp_path / "a.petsc"), str(tmp_path / "b.petsc")
+    api.write_petsc_binary_matrix(a, n, n, rp, col, val)
+    assert api.write_powerlaw_petsc(b, n) == rp[-1]
+    with open(a, "rb") as fa, open(b, "rb") as fb:
+        assert fa.read() == fb.read()
+    with pytest.raises(RuntimeError):
+        api.write_powerlaw_petsc(str(tmp_path / "no_such_dir" / "c.petsc"), 100)
