@@ -9,6 +9,7 @@
 // convergence test runs on the device and sets a `done` flag that turns every later
 // kernel into a no-op; the host reads the flag LOOKAHEAD iterations behind, so the
 // iteration count and x are exactly those of the reference's loop.
+#include <cstdlib>
 #include "cg.h"
 
 #include "L2GMap.h"
@@ -119,6 +120,19 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
       single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
     if (single && (single->non_zeros() == 0 || single->op().plan() == nullptr))
       single = nullptr;
+    // The epilogue pays only where the SpMV instantiation keeps its occupancy with the extra
+    // registers: stencil-length rows (16-entry walk; 27-point 256^3: 1.157 vs 1.150 ms/iteration,
+    // one launch fewer).  With short rows the dot-carrying 8-entry walk loses a resident CTA per
+    // SM and a separate 31 us dot kernel wins (7-point general 256^3: 0.74 -> 0.56 ms/iteration,
+    // profiles/r01_cg_fused_dot_ab.txt).  B200_CG_FUSED_DOT=0/1 forces either.
+    if (single) {
+      const double mean_row = (double)single->non_zeros() / (double)std::max(M, 1);
+      bool fused = mean_row > 10.0;
+      if (const char* e = std::getenv("B200_CG_FUSED_DOT"))
+        fused = *e != '0';
+      if (!fused)
+        single = nullptr;
+    }
 
     bool stop = false;
     for (int k = 0; k < kmax && !stop; ++k) {

@@ -991,15 +991,26 @@ static void plan_choose_walk(Plan* p)
     p->walk = mean <= 10.0 ? WALK_ROW8 : WALK_ROW16;
 }
 
-// Launch shape that measured best for each walk (tile bytes, consumer warps, CTAs/SM).
-static void plan_default_shape(const Plan* p, int* tile_bytes, int* cw, int* ctas)
+// Launch shape that measured best for each walk (tile bytes, pipeline stages, consumer warps,
+// CTAs/SM).  More than two stages only pays for the symmetric 4-entry walk, whose gathers are
+// mostly served from the staged x slice: everywhere else the shared memory taken from L1 costs
+// more than the deeper pipeline gives (profiles/r01_exp_za_probe3_stage_sweep.txt,
+// r01_stage_sweep_head.txt: 27-point general 0.85 -> 1.05 ms with 3 stages).
+static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int* cw, int* ctas)
 {
+  *stages = 2;
   switch (p->walk) {
   case WALK_ROW4:
-    *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
+    if (p->symmetric)
+      *tile_bytes = 20 * 1024, *stages = 3, *cw = 16, *ctas = 2; // sym 7-pt 0.222 -> 0.215 ms
+    else
+      *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
     break;
   case WALK_ROW8:
-    *tile_bytes = 24 * 1024, *cw = 8, *ctas = p->symmetric ? 3 : 4;
+    if (p->symmetric)
+      *tile_bytes = 32 * 1024, *cw = 8, *ctas = 3; // sym 27-pt 0.702 -> 0.634 ms
+    else
+      *tile_bytes = 24 * 1024, *cw = 8, *ctas = 4;
     break;
   case WALK_STREAM:
   case WALK_SEG:
@@ -1327,10 +1338,10 @@ int b200_csr_plan_create(void** plan, int32_t rows, int32_t cols, int64_t nnz,
   const int variant = env_int("B200_SPMV_VARIANT", 0);
   p->walk_forced = walk_of_variant(variant);
   plan_choose_walk(p);
-  int d_tile, d_cw, d_ctas;
-  plan_default_shape(p, &d_tile, &d_cw, &d_ctas);
+  int d_tile, d_stages, d_cw, d_ctas;
+  plan_default_shape(p, &d_tile, &d_stages, &d_cw, &d_ctas);
   rc = plan_apply_tuning(p, variant, env_int("B200_SPMV_TILE_BYTES", d_tile),
-                         env_int("B200_SPMV_STAGES", 2), env_int("B200_SPMV_CWARPS", d_cw),
+                         env_int("B200_SPMV_STAGES", d_stages), env_int("B200_SPMV_CWARPS", d_cw),
                          env_int("B200_SPMV_CTAS", d_ctas));
   if (rc)
     return fail(rc);
