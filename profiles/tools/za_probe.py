@@ -1,6 +1,8 @@
 #!/usr/bin/env python
-"""za_probe.py -- symmetric SpMV with y zeroed inside the kernel (zero-ahead) against the memset pass:
-timing, agreement of the two results, NaN-poisoned y before every checked run (coverage of the zero-fill)."""
+"""za_probe.py -- sweeper for the symmetric SpMV: zero-ahead of y (B200_SPMV_ZA) against the memset pass and
+launch shapes.  ZA_CONFIGS = comma list of za:k:d[:stages[:tile_bytes[:cwarps[:ctas]]]] (k tiles per chunk, d chunks
+of lead); every config is timed, compared with the first one and run on NaN-poisoned y (coverage of the zero-fill).
+ZA_GCONFIGS = stages:tile:cw:ctas shapes for the general-storage kernel of the same stencil."""
 import os
 import sys
 
@@ -36,13 +38,13 @@ def main():
         nnz = int(ci.numel())
         nbytes = 12 * nnz + 4 * (N + 1) + 24 * N
         res = {}
-        configs = [c.split(":") for c in os.environ.get("ZA_CONFIGS", "0:4:0,1:4:0,0:4:1,1:4:1,1:8:1").split(",")]
+        configs = [c.split(":") for c in os.environ.get("ZA_CONFIGS", "0:4:2,1:4:2,1:4:4").split(",")]
         for cfg in configs:
-            za, k, xwin = cfg[:3]
+            za, k, d = cfg[:3]
             os.environ["B200_SPMV_ZA"] = za
             os.environ["B200_SPMV_ZA_K"] = k
-            os.environ["B200_SPMV_XWIN"] = xwin
-            for name, val in zip(("STAGES", "TILE_BYTES", "CWARPS", "CTAS"), list(cfg[3:]) + [""] * 4):
+            os.environ["B200_SPMV_ZA_D"] = d
+            for name, val in zip(("STAGES", "TILE_BYTES", "CWARPS", "CTAS"), list(cfg[3:7]) + [""] * 4):
                 if val:
                     os.environ["B200_SPMV_" + name] = val
                 else:
