@@ -2,7 +2,10 @@
 """za_probe.py -- sweeper for the symmetric SpMV: zero-ahead of y (B200_SPMV_ZA) against the memset pass and
 launch shapes.  ZA_CONFIGS = comma list of za:k:d[:stages[:tile_bytes[:cwarps[:ctas]]]] (k tiles per chunk, d chunks
 of lead); every config is timed, compared with the first one and run on NaN-poisoned y (coverage of the zero-fill).
-ZA_GCONFIGS = stages:tile:cw:ctas shapes for the general-storage kernel of the same stencil."""
+ZA_GCONFIGS = stages:tile:cw:ctas shapes for the general-storage kernel of the same stencil.
+The za / k / d fields only act on a build with profiles/r01_exp_zero_ahead_lead.patch applied (the product has no
+zero-ahead path: measured slower, profiles/r01_sym7_supply.md); on the product build they are ignored and the tool
+is a launch-shape sweeper."""
 import os
 import sys
 
