@@ -578,6 +578,13 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
 
   if (warp == CW) {
     if (lane == 0) {
+      const uint64_t pol_stream = SYM ? l2_policy_evict_first() : 0ull;
+      auto stream_g2s = [&](void* d, const void* g, uint32_t bytes, uint64_t* bar) {
+        if constexpr (SYM)
+          bulk_g2s_hint(d, g, bytes, bar, pol_stream);
+        else
+          bulk_g2s(d, g, bytes, bar);
+      };
       for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
         if (use > 0)
           mbar_wait(empty + s, (use - 1) & 1);
@@ -603,13 +610,18 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
           const TileLayout<T, LAY> L(r0, ns, lo, hi);
           unsigned char* dst = smem + (size_t)s * sb;
           mbar_arrive_expect_tx(full + s, (uint32_t)L.loaded());
+          // Symmetric storage: the matrix is read once per SpMV, while the y lines are touched several
+          // times (zero-fill, the row's own add, the adds from the rows that list it).  evict_first on
+          // the matrix stream keeps it from displacing them in L2: sym 7-pt 0.220 -> 0.213 ms, sym 27-pt
+          // 0.64 -> 0.62 (profiles/r01_exp_evict_first_probe.txt).  General storage gains nothing
+          // (7-pt 0.2526 vs 0.2515, 27-pt 0.864 vs 0.849) and keeps the default policy.
           if (L.bytes_v > 0)
-            bulk_g2s(dst, a.val + L.lo_v, L.bytes_v, full + s);
+            stream_g2s(dst, a.val + L.lo_v, L.bytes_v, full + s);
           if (L.bytes_c > 0)
-            bulk_g2s(dst + L.off_c(), a.colind + L.lo_c, L.bytes_c, full + s);
-          bulk_g2s(dst + L.off_r(), a.rowptr + L.lo_r, L.bytes_r, full + s);
+            stream_g2s(dst + L.off_c(), a.colind + L.lo_c, L.bytes_c, full + s);
+          stream_g2s(dst + L.off_r(), a.rowptr + L.lo_r, L.bytes_r, full + s);
           if (LAY >= LAY_DX) {
-            bulk_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
+            stream_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
             bulk_g2s(dst + L.off_x(), a.x + L.lo_d, L.bytes_d, full + s);
           }
         } else {
