@@ -145,8 +145,10 @@ class Operator:
         self.x = torch.zeros(self.ncols, dtype=torch.float64, device=dev)
         self.x[: self.rows] = torch.from_numpy(synth.bump_vector(n_glob, row0, row0 + self.rows)).to(dev)
         self.y = torch.empty(self.rows, dtype=torch.float64, device=dev)
-        # our kernels per step: pack (if neighbours) + local block + remote block (if it has entries)
-        self.launches_per_step = (1 if self.nnbr else 0) + 1 + (1 if self.nnz_remote > 0 else 0)
+        # our kernels per step: pack (if neighbours) + local block (symmetric storage: + the zero-fill of y,
+        # zero_fill_desc_kernel) + remote block (if it has entries)
+        self.launches_per_step = ((1 if self.nnbr else 0) + 1 + (1 if symmetric else 0)
+                                  + (1 if self.nnz_remote > 0 else 0))
 
     def nnz_full(self):
         if self.symmetric:
@@ -465,7 +467,7 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",
                      "frac": head["frac_of_hbm_peak"], "traffic": TRAFFIC_NCU.get("sym7"),
                      "kernel": "spmv_pipe_kernel<double, SYM, ROW4S> (local block; the event pair also spans the "
-                               "zero-fill of y that precedes it)",
+                               "zero-fill of y, zero_fill_desc_kernel, that precedes it)",
                      "kernel_ms_avg": head["kernel_ms_avg"], "kernel_ms_min": head["kernel_ms_min"],
                      "algorithmic_bytes": bytes_symmetric(cfg["stored_nnz_per_gpu"] if size == 1 else 0, 0,
                                                           cfg["rows_per_gpu"], 0) if size == 1 else None,

@@ -818,6 +818,21 @@ __global__ void diag_only_kernel(int n, const T* __restrict__ diag, const T* __r
   }
 }
 
+// Zero-fill of y in front of the symmetric kernel (beta == 0), instead of cudaMemsetAsync: from
+// the LAST row down to the first and with an evict_last L2 policy, so that what is still in L2
+// when the walk starts at row 0 is the low end of y, and the matrix stream (evict_first) does
+// not push it out before the adds arrive.  n16 = number of 16-byte units.
+__global__ void zero_fill_desc_kernel(size_t n16, float4* __restrict__ y)
+{
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n16; k += stride)
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %1, %1, %1}, %2;" ::"l"(y + (n16 - 1 - k)), "f"(0.f),
+                 "l"(pol)
+                 : "memory");
+}
+
 template <typename T>
 __global__ void scale_kernel(int n, T beta, T* __restrict__ y)
 {
@@ -1183,9 +1198,19 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
       return B200_OK;
     }
     // every write below is an add: bring y to beta*y first
-    if (beta == T(0))
-      B200_CUDA(cudaMemsetAsync(d_y, 0, sizeof(T) * (size_t)p.rows, st));
-    else if (beta != T(1)) {
+    if (beta == T(0)) {
+      static const int zfill = env_int("B200_SPMV_ZFILL", 1);
+      const size_t bytes = sizeof(T) * (size_t)p.rows;
+      if (zfill && aligned16(d_y) && bytes >= (1u << 16)) {
+        const size_t n16 = bytes / 16;
+        zero_fill_desc_kernel<<<num_sms() * 8, 256, 0, st>>>(n16, reinterpret_cast<float4*>(d_y));
+        B200_LAUNCH_CHECK();
+        if (bytes > n16 * 16)
+          B200_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(d_y) + n16 * 16, 0, bytes - n16 * 16, st));
+      } else {
+        B200_CUDA(cudaMemsetAsync(d_y, 0, bytes, st));
+      }
+    } else if (beta != T(1)) {
       scale_kernel<T><<<gb, tb, 0, st>>>(p.rows, beta, d_y);
       B200_LAUNCH_CHECK();
     }
