@@ -481,7 +481,8 @@ def run_b200(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
 # (profiles/): filled in when a capture of the current kernel exists, else null.
-TRAFFIC_NCU = {"sym7": 1072724000 + 106889216}  # profiles/r01_sym7_final_ncu_summary.txt (3 stages x 20 KB, evict_first)
+TRAFFIC_NCU = {"sym7": 1072455000 + 106979584}  # profiles/r01_sym7_final_ncu_summary.txt (ncu flushes L2 before
+# each replay, so this is the cold-cache figure: in the bench loop part of y is still in L2 from the zero-fill kernel)
 
 
 # ----------------------------------------------------------------------------
