@@ -201,6 +201,22 @@ def test_laplace_symmetric(cuda, tune):
     assert rel_l2(y, OK.spmv(rp, col, val, x)) < TOL  # same operator as the full storage
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, TOL), (torch.float32, 1e-5)])
+def test_symmetric_zero_fill_odd_rows(cuda, dtype, tol):
+    """beta == 0 on NaN-poisoned y with an odd row count above the size where y is zeroed by
+    zero_fill_desc_kernel (16-byte units from the end + a tail of less than 16 bytes)."""
+    nx, ny, nz = 21, 21, 43  # 18963 rows: 151704 B (fp64), 75852 B (fp32), neither a multiple of 16
+    N = nx * ny * nz
+    rp, col, val = synth.laplace3d_rows(nx, ny, nz, 0, nz, 7)
+    srp, sci, sv, d = split_symmetric(rp, col, val)
+    x = synth.bump_vector(N, 0, N)
+    if dtype == torch.float32:
+        x, sv, d = x.astype(np.float32), sv.astype(np.float32), d.astype(np.float32)
+    y = run_sym(cuda, srp, sci, sv, d, x, dtype=dtype)
+    assert np.isfinite(y).all()
+    assert rel_l2(y, OK.symv(srp, sci, sv, d, x)) < tol
+
+
 @pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.5, 1.0), (-1.5, 0.25)])
 def test_random_symmetric(cuda, alpha, beta):
     rng = np.random.default_rng(5)
