@@ -38,6 +38,10 @@ def parse():
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling (BASELINE configs[2]): the 256^3 grid split over the GPUs, nz = 256 / N")
     ap.add_argument("--no-extras", action="store_true", help="skip the 'also' measurements and cpu_baseline")
+    ap.add_argument("--with-cusparse", action="store_true",
+                    help="N=1 only: also time cusparseSpMV (through torch.sparse CSR) on the 27-point operator -- "
+                         "what the reference's CUDA backend runs (cuda/csr_kernels.cuda.cu:106-151); context, not a leg "
+                         "of the contract")
     ap.add_argument("--config5-rows", type=int, default=CONFIG5_ROWS_PER_GPU,
                     help="rows per GPU of the power-law / PETSc leg (default 6.25 M = 50 M rows at 8 GPUs; 0 skips it)")
     return ap.parse_args()
@@ -452,6 +456,8 @@ def run_b200(args):
         also["cg_sym_7pt"] = measure_cg(api, ops, timer, dev, size)
         ops.close()
         del ops
+        if args.with_cusparse and size == 1:
+            also["cusparse_general_27pt"] = measure_cusparse(dev, nz)
         # ---- config 5: power-law rows through the PETSc reader --------------------------
         if args.config5_rows > 0:
             also["powerlaw_petsc"] = measure_config5(api, ex, dev, rank, size, timer, peak, args.config5_rows)
@@ -477,6 +483,35 @@ def run_b200(args):
     if size == 1 and not args.no_extras:
         line["cpu_baseline"] = cpu_baseline()
     print(json.dumps(line), file=_JSON_OUT, flush=True)
+
+
+def measure_cusparse(dev, nz, steps=20, warmup=3):
+    """cusparseSpMV on the general 27-point operator via torch.sparse (int32 indices, fp64), CUDA events.  Library
+    code, opt-in, for context only: the reference's CUDA backend calls the same routine."""
+    try:
+        import torch
+        from spmv_b200 import kernels as K
+        from spmv_b200 import synth
+        g = K.laplace3d(NX, NY, nz, 0, nz, 27, 0, dev)
+        rp, ci, v = g["local"]
+        n = NX * NY * nz
+        A = torch.sparse_csr_tensor(rp, ci, v, size=(n, n))
+        x = torch.from_numpy(synth.bump_vector(n, 0, n)).to(dev)
+        for _ in range(warmup):
+            y = A.matmul(x)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            y = A.matmul(x)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        nbytes = bytes_general(int(ci.numel()), 0, n, n, False)
+        del A, y, g
+        return {"ms_per_step": ms, "GBps": nbytes / ms / 1e6, "how": "torch.sparse_csr_tensor(int32, fp64).matmul -> cusparseSpMV"}
+    except Exception as e:  # opt-in context measurement: never fail the bench over it
+        return {"error": str(e)[:200]}
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
