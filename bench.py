@@ -254,6 +254,56 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
     return out
 
 
+def laplace_parity(op, rank, size, nz, stencil, dev, planes=4):
+    """In-run parity of a Laplacian leg at bench size and at every N: regenerate sampled z-planes of THIS
+    rank's rows on the host (synth.laplace3d_rows gives any plane range with global columns; x is a formula
+    of the global index, so ghost values are known too), sum each row left to right in fp64
+    (csr_kernels.cpp:42-49) and compare with the y the timed loop left on the device.  The first and last
+    plane of the slab are always in the sample: those are the rows that read ghosts.  Raises above 1e-12
+    (BASELINE tolerance: relative L2)."""
+    import numpy as np
+    import torch
+    from spmv_b200 import synth
+    plane = NX * NY
+    nzg = nz * size
+    n_glob = plane * nzg
+    z0 = rank * nz
+    rng = np.random.default_rng(20261105 + rank)
+    zs = sorted({z0, z0 + nz - 1, z0 + nz // 2, z0 + int(rng.integers(0, nz))})[:max(planes, 2)]
+    op.step()  # y = A x for the x of this operator
+    y = op.y
+    num = den = 0.0
+    worst_row = 0.0
+    for z in zs:
+        rp, col, val = synth.laplace3d_rows(NX, NY, nzg, z, z + 1, stencil)
+        xs = np.exp(-10.0 * np.power(5.0 * (col.astype(np.float64) / float(n_glob) - 0.5), 2.0))
+        prod = val * xs
+        want = np.zeros(plane)
+        cnt = np.diff(rp)
+        for j in range(int(cnt.max())):  # left to right, one entry of every row at a time
+            m = cnt > j
+            want[m] += prod[rp[:-1][m] + j]
+        got = y[(z - z0) * plane:(z - z0 + 1) * plane].cpu().numpy()
+        num += float(np.sum((got - want) ** 2))
+        den += float(np.sum(want ** 2))
+        scale = np.maximum(np.abs(want), np.abs(want).max() * 1e-30 + 1e-300)
+        worst_row = max(worst_row, float(np.max(np.abs(got - want) / scale)))
+    t = torch.tensor([num, den], dtype=torch.float64, device=dev)
+    w = torch.tensor([worst_row], dtype=torch.float64, device=dev)
+    if size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+    rel = float(torch.sqrt(t[0] / t[1]).item()) if float(t[1].item()) > 0 else float("nan")
+    out = {"rel_l2": rel, "max_rel_err_row": float(w.item()), "rows_checked_per_rank": len(zs) * plane,
+           "planes_per_rank": [int(z - z0) for z in zs], "tolerance": 1e-12,
+           "how": "sampled z-planes (first, last, middle, one random) of every rank regenerated on the host, "
+                  "left-to-right fp64 row sums, relative L2 over all ranks' samples"}
+    if not rel <= 1e-12:
+        raise RuntimeError(f"{stencil}-point Laplacian: y differs from the regenerated rows, rel L2 {rel}")
+    return out
+
+
 def measure_config5(api, ex, dev, rank, size, timer, peak, rows_per_gpu):
     """BASELINE configs[4]: irregular power-law rows, written as a PETSc binary file by the host-core
     generator (demos/CreatePowerLaw.h), read back with read_petsc_binary_matrix, general CSR SpMV
@@ -349,10 +399,27 @@ def measure_cg(api, op, timer, dev, size):
 
     ms = timer.run(solve, 1)
     hist = holder["hist"]
+
+    def gsum(v):  # sum over the ranks of a device scalar
+        if size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(v)
+        return float(v.item())
+
+    bnorm = gsum(torch.dot(b, b)) ** 0.5
+    # ||b - A x|| / ||b|| recomputed with one more SpMV: the recurrence's residual can drift from the true one
+    xp = torch.zeros(op.ncols, dtype=torch.float64, device=dev)
+    xp[:M] = xs
+    ax = torch.empty(M, dtype=torch.float64, device=dev)
+    op.col_map.update(xp)
+    op.A.mult(xp, ax)
+    rtrue = gsum(torch.dot(b - ax, b - ax)) ** 0.5 / bnorm
     res["solve_rtol_1e-8"] = {"iterations": int(holder["it"]), "ms": ms,
                               "iters_per_s": holder["it"] / (ms * 1e-3) if ms > 0 else None,
-                              "final_rel_residual": float(hist[-1] / (b.norm().item() if size == 1 else 1.0))
-                              if len(hist) and size == 1 else None}
+                              "final_rel_residual": float(hist[-1] / bnorm) if len(hist) else None,
+                              "residual_true": rtrue, "converged": bool(len(hist) and hist[-1] / bnorm < 1e-8)}
+    if not rtrue < 1e-6:
+        raise RuntimeError(f"CG: true residual {rtrue} after {holder['it']} iterations")
     return res
 
 
@@ -420,6 +487,7 @@ def run_b200(args):
         sampler.start()
         time.sleep(0.3)
     head = measure_spmv(op, timer, args.steps, args.warmup, peak, with_e2e=True)
+    head_parity = laplace_parity(op, rank, size, nz, 7, dev)
     # keep the GPUs busy ~1 s longer so the 100 ms sampler sees the loaded clocks (same count on
     # every rank: the step time is already the max over ranks)
     for _ in range(int(min(1000.0 / max(head["ms_per_step"], 1e-3), 20000))):
@@ -442,7 +510,7 @@ def run_b200(args):
         # ---- general 27-point SpMV (the case the roofline target is quoted on) -----------
         op27 = Operator(api, ex, dev, rank, size, nz, 27, False)
         g = measure_spmv(op27, timer, 30, 5, peak, with_e2e=True)
-        also["general_27pt_spmv"] = {"GBps": g["GBps"], "ms_per_step": g["ms_per_step"], "GFLOPs": g["GFLOPs"],
+        also["general_27pt_spmv"] = {"parity": laplace_parity(op27, rank, size, nz, 27, dev), "GBps": g["GBps"], "ms_per_step": g["ms_per_step"], "GFLOPs": g["GFLOPs"],
                                      "kernel_ms_avg": g["kernel_ms_avg"], "kernel_ms_min": g["kernel_ms_min"],
                                      "kernel_ms_median": g["kernel_ms_median"], "kernel_GBps": g["kernel_GBps"],
                                      "frac_of_hbm_peak": g["frac_of_hbm_peak"], "e2e": g["e2e"],
@@ -469,7 +537,7 @@ def run_b200(args):
         "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True,
         "scaling": "strong" if args.strong else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "e2e": head["e2e"],
-        "gpu_launches": head_launches, "clocks": clocks,
+        "gpu_launches": head_launches, "clocks": clocks, "parity": head_parity,
         "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",
                      "frac": head["frac_of_hbm_peak"], "traffic": TRAFFIC_NCU.get("sym7"),
                      "kernel": "spmv_pipe_kernel<double, SYM, ROW4S> (local block; the event pair also spans the "

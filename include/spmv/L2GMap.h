@@ -128,6 +128,11 @@ private:
   std::vector<size_t> _peer_slot_bytes;
   std::vector<std::int64_t> _land;   // per neighbour: element offset of my slice in its ghost tail
   mutable std::uint32_t _epoch = 0;
+  // reverse direction (reverse_update): two more slots of _num_indices elements + flags behind the forward ones
+  size_t _rev_base = 0, _rev_slot_bytes = 0;
+  std::vector<size_t> _peer_rev_base, _peer_rev_slot_bytes;
+  std::vector<std::int64_t> _rev_land; // per neighbour: element offset of my slice in its reverse slot
+  mutable std::uint32_t _rev_epoch = 0;
   // scalar allreduce over peer memory (CG): my mailbox, everyone's as mapped here, device descriptor
   char* _ar_box = nullptr;
   std::vector<void*> _ar_boxes;

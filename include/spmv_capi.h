@@ -85,6 +85,22 @@ SPMVH_API int spmvh_matrix_mult_host_f64(void* mat, const double* x_host, double
 SPMVH_API int spmvh_matrix_tune(void* mat, int which, int variant, int tile_bytes, int stages, int consumer_warps,
                                 int ctas_per_sm);
 
+/* ---- fp32 twins: Matrix<float>, L2GMap::update<float> (the reference instantiates both: Matrix.cpp:565,
+ *      L2GMap.cpp:1001,1007,1012).  A float matrix handle is only valid with the *_f32 entries; maps are
+ *      untyped and take either update. ---- */
+SPMVH_API int spmvh_l2g_update_f32(void* map, float* d_vec);
+SPMVH_API int spmvh_l2g_update_finalise_f32(void* map, float* d_vec);
+SPMVH_API int spmvh_l2g_reverse_update_f32(void* map, float* d_vec);
+SPMVH_API int spmvh_matrix_create_f32(void** mat, void* exec, const int32_t* rowptr, const int32_t* colind,
+                                      const float* values, int64_t nrows_local, int64_t ncols_local,
+                                      const int64_t* row_ghosts, int64_t num_row_ghosts, const int64_t* col_ghosts,
+                                      int64_t num_col_ghosts, int symmetric, int cm);
+SPMVH_API int spmvh_matrix_destroy_f32(void* mat);
+SPMVH_API int spmvh_matrix_info_f32(void* mat, int64_t out[8]);
+SPMVH_API int spmvh_matrix_col_map_f32(void* mat, void** map);
+SPMVH_API int spmvh_matrix_mult_f32(void* mat, float* d_x, float* d_y);
+SPMVH_API int spmvh_matrix_mult_host_f32(void* mat, const float* x_host, float* y_host);
+
 /* ---- spmv::cg.  hist (may be NULL) receives ||r_k||, k = 1..iterations. ---- */
 SPMVH_API int spmvh_cg(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol, double* hist,
                        int hist_cap, int* iterations);

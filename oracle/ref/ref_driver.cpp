@@ -6,6 +6,8 @@
 // -fno-access-control so the private halo plan can be read without touching the
 // reference sources.  Ranks are threads: every call acts on the calling thread's
 // MPI_COMM_WORLD (drive them with ref_run_ranks).
+#include <chrono>
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -13,6 +15,7 @@
 #include <vector>
 
 #include <mpi.h>
+#include <cblas.h>
 
 #include "L2GMap.h"
 #include "Matrix.h"
@@ -221,6 +224,44 @@ int ref_update(void* h, double* x)
 int ref_mult(void* h, double* x, double* y)
 {
   return guarded([&] { static_cast<RefMat*>(h)->mat->mult(x, y); });
+}
+// L2GMap::reverse_update (L2GMap.cpp:908-959; only the collective_blocking variant is safe to run:
+// the p2p one writes 2*nbrs requests into a _req sized nbrs)
+int ref_reverse_update(void* h, double* x)
+{
+  return guarded([&] { static_cast<RefMat*>(h)->mat->_col_map->reverse_update(x); });
+}
+// The timed loop of demos/spmv.cpp:81-103 on this thread-rank: warm-up, then n_apply x {barrier; update;
+// barrier; mult; barrier; x <- y}, wall-clock per phase accumulated like the demo's `timings` map
+// (seconds: t[0] update, t[1] mult, t[2] copy), and the final ||x||_2 of demos/spmv.cpp:105-108.
+int ref_demo_spmv_loop(void* h, double* x, double* y, int n_apply, double t[3], double* xnorm)
+{
+  return guarded([&] {
+    auto* m = static_cast<RefMat*>(h);
+    const int M = m->mat->rows();
+    auto l2g = m->mat->col_map();
+    using clk = std::chrono::steady_clock;
+    t[0] = t[1] = t[2] = 0.0;
+    l2g->update(x);
+    m->mat->mult(x, y);
+    for (int i = 0; i < n_apply; ++i) {
+      MPI_Barrier(MPI_COMM_WORLD);
+      auto a = clk::now();
+      l2g->update(x);
+      t[0] += std::chrono::duration<double>(clk::now() - a).count();
+      MPI_Barrier(MPI_COMM_WORLD);
+      a = clk::now();
+      m->mat->mult(x, y);
+      t[1] += std::chrono::duration<double>(clk::now() - a).count();
+      MPI_Barrier(MPI_COMM_WORLD);
+      a = clk::now();
+      m->exec->copy<double>(x, y, M);
+      t[2] += std::chrono::duration<double>(clk::now() - a).count();
+    }
+    double local = cblas_ddot(M, x, 1, x, 1), glob = 0.0;
+    MPI_Allreduce(&local, &glob, 1, MPI_DOUBLE, MPI_SUM, MPI_COMM_WORLD);
+    *xnorm = std::sqrt(glob);
+  });
 }
 // spmv::cg (cg.cpp:21-98)
 int ref_cg(void* h, const double* b, double* x, int kmax, double rtol, int* iterations)

@@ -44,6 +44,8 @@ def lib():
             "ref_update": [_p, _p],
             "ref_mult": [_p, _p, _p],
             "ref_cg": [_p, _p, _p, _int, _f64, C.POINTER(_int)],
+            "ref_reverse_update": [_p, _p],
+            "ref_demo_spmv_loop": [_p, _p, _p, _int, C.POINTER(_f64), C.POINTER(_f64)],
         }
         for n, a in sig.items():
             f = getattr(L, n)
@@ -173,6 +175,17 @@ class RefMatrix:
 
     def mult(self, x, y):
         _ck(lib().ref_mult(self.h, _ptr(x), _ptr(y)))
+
+    def reverse_update(self, x):
+        """L2GMap::reverse_update on the column map (use cm = collective_blocking)."""
+        _ck(lib().ref_reverse_update(self.h, _ptr(x)))
+
+    def demo_spmv_loop(self, x, y, n_apply=100):
+        """demos/spmv.cpp:81-108 -> ({"update": s, "mult": s, "copy": s}, final ||x||_2); x, y are updated."""
+        t = (_f64 * 3)()
+        nrm = _f64()
+        _ck(lib().ref_demo_spmv_loop(self.h, _ptr(x), _ptr(y), int(n_apply), t, C.byref(nrm)))
+        return {"update": t[0], "mult": t[1], "copy": t[2]}, nrm.value
 
     def cg(self, b, kmax, rtol):
         b = np.ascontiguousarray(b, dtype=np.float64)

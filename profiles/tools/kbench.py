@@ -56,9 +56,16 @@ def powerlaw(a, dev):
     variants = [int(v) for v in os.environ.get("KB_VARIANTS", "2,3,4,6").split(",")]
     for variant in variants:
         shapes = [(24576, 2, 8, 3), (24576, 2, 16, 2), (49152, 2, 8, 2), (49152, 2, 16, 2), (32768, 2, 8, 3)]
-        if variant in (3, 6):
+        if variant == 3:
             shapes += [(16384, 2, 16, 2), (16384, 2, 16, 3), (24576, 2, 16, 3), (16384, 3, 16, 3), (24576, 3, 16, 2),
                        (24576, 3, 8, 4), (12288, 2, 16, 3), (12288, 3, 16, 3), (49152, 3, 16, 1), (20480, 2, 16, 3)]
+        if variant in (6, 7):  # warp-private pipelined walk: register-bound at 2 CTAs (16 warps) / 3 CTAs (8 warps)
+            shapes = [(24576, 2, 16, 2), (24576, 3, 16, 2), (16384, 2, 16, 2), (16384, 3, 16, 2), (16384, 4, 16, 2),
+                      (12288, 3, 16, 2), (12288, 4, 16, 2), (8192, 4, 16, 2), (8192, 6, 16, 2), (32768, 3, 16, 2),
+                      (49152, 2, 16, 1), (49152, 3, 16, 1), (32768, 4, 16, 1),
+                      (16384, 3, 8, 3), (12288, 3, 8, 3), (8192, 4, 8, 3), (24576, 2, 8, 3), (24576, 3, 8, 2)]
+        if os.environ.get("KB_SHAPES"):
+            shapes = [tuple(int(t) for t in sh.split("x")) for sh in os.environ["KB_SHAPES"].split(",")]
         for tb, stg, cw, ct in shapes:
             plan.tune(variant, tb, stg, cw, ct)
             ms = timeit(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y), a)

@@ -62,6 +62,15 @@ _SIG = {
     "spmvh_l2g_allreduce_f64": [_p, _p, _i32, C.c_int],
     "spmvh_matrix_tune": [_p, _int, _int, _int, _int, _int, _int],
     "spmvh_cg": [_p, _p, _p, _p, _int, _f64, _p, _int, C.POINTER(_int)],
+    "spmvh_l2g_update_f32": [_p, _p],
+    "spmvh_l2g_update_finalise_f32": [_p, _p],
+    "spmvh_l2g_reverse_update_f32": [_p, _p],
+    "spmvh_matrix_create_f32": [_pp, _p, _p, _p, _p, _i64, _i64, _p, _i64, _p, _i64, _int, _int],
+    "spmvh_matrix_destroy_f32": [_p],
+    "spmvh_matrix_info_f32": [_p, C.POINTER(_i64)],
+    "spmvh_matrix_col_map_f32": [_p, _pp],
+    "spmvh_matrix_mult_f32": [_p, _p, _p],
+    "spmvh_matrix_mult_host_f32": [_p, _p, _p],
     "spmvh_write_petsc_matrix": [C.c_char_p, _i32, _i32, _p, _p, _p],
     "spmvh_write_petsc_vector": [C.c_char_p, _i32, _p],
     "spmvh_read_petsc_vector": [_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(_i64)],
@@ -346,14 +355,19 @@ class L2GMap:
         d.update(local_size=s[0], num_ghosts=s[1], global_size=s[2], global_offset=s[3])
         return d
 
+    @staticmethod
+    def _sfx(vec):
+        """L2GMap::update<T> is a template: the tensor's dtype picks the instantiation."""
+        return "f32" if str(getattr(vec, "dtype", "")).endswith("float32") else "f64"
+
     def update(self, vec):
-        _ck(host_lib().spmvh_l2g_update_f64(self.h, _dev_ptr(vec)))
+        _ck(getattr(host_lib(), "spmvh_l2g_update_" + self._sfx(vec))(self.h, _dev_ptr(vec)))
 
     def update_finalise(self, vec):
-        _ck(host_lib().spmvh_l2g_update_finalise_f64(self.h, _dev_ptr(vec)))
+        _ck(getattr(host_lib(), "spmvh_l2g_update_finalise_" + self._sfx(vec))(self.h, _dev_ptr(vec)))
 
     def reverse_update(self, vec):
-        _ck(host_lib().spmvh_l2g_reverse_update_f64(self.h, _dev_ptr(vec)))
+        _ck(getattr(host_lib(), "spmvh_l2g_reverse_update_" + self._sfx(vec))(self.h, _dev_ptr(vec)))
 
     def allreduce_sum(self, vec, nccl=False):
         """Sum the (<= 4) doubles of `vec` over the ranks, in place, on the executor's stream."""
@@ -461,6 +475,60 @@ class Matrix:
         self._col = self._row = None
         if self.h:
             host_lib().spmvh_matrix_destroy(self.h)
+            self.h = None
+
+
+class MatrixF32:
+    """spmv::Matrix<float> (Matrix.cpp:565): create_matrix, col_map, mult, mult_host on float32 vectors."""
+
+    def __init__(self, handle, exec):
+        self.h, self.exec, self._col = handle, exec, None
+
+    @staticmethod
+    def create_matrix(exec, rowptr, colind, values, nrows_local, ncols_local, row_ghosts, col_ghosts,
+                      symmetric=False, cm=COLLECTIVE_BLOCKING):
+        rp = np.ascontiguousarray(rowptr, dtype=np.int32)
+        ci = np.ascontiguousarray(colind, dtype=np.int32)
+        v = np.ascontiguousarray(values, dtype=np.float32)
+        rg = np.ascontiguousarray(row_ghosts, dtype=np.int64)
+        cg = np.ascontiguousarray(col_ghosts, dtype=np.int64)
+        h = C.c_void_p()
+        _ck(host_lib().spmvh_matrix_create_f32(C.byref(h), exec.h, _np_ptr(rp), _np_ptr(ci), _np_ptr(v),
+                                               int(nrows_local), int(ncols_local), _np_ptr(rg), len(rg), _np_ptr(cg),
+                                               len(cg), int(bool(symmetric)), int(cm)))
+        return MatrixF32(h, exec)
+
+    def _info(self):
+        out = (_i64 * 8)()
+        _ck(host_lib().spmvh_matrix_info_f32(self.h, out))
+        return list(out)
+
+    def rows(self):
+        return self._info()[0]
+
+    def non_zeros(self):
+        return self._info()[2]
+
+    def col_map(self):
+        if self._col is None:
+            h = C.c_void_p()
+            _ck(host_lib().spmvh_matrix_col_map_f32(self.h, C.byref(h)))
+            self._col = L2GMap(_handle=h)
+        return self._col
+
+    def mult(self, x, y):
+        _ck(host_lib().spmvh_matrix_mult_f32(self.h, _dev_ptr(x), _dev_ptr(y)))
+
+    def mult_host(self, x_host, y_host):
+        assert x_host.dtype == np.float32 and y_host.dtype == np.float32
+        _ck(host_lib().spmvh_matrix_mult_host_f32(self.h, _np_ptr(x_host), _np_ptr(y_host)))
+
+    def close(self):
+        if self._col is not None:
+            self._col.close()
+            self._col = None
+        if self.h:
+            host_lib().spmvh_matrix_destroy_f32(self.h)
             self.h = None
 
 

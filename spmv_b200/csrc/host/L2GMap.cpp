@@ -139,20 +139,33 @@ void L2GMap::setup_peer_halo()
   struct Card {
     char handle[B200_IPC_HANDLE_BYTES];
     std::int64_t slot_bytes;
+    std::int64_t rev_base;
+    std::int64_t rev_slot_bytes;
     std::int64_t ok;
   };
   Card mine;
   std::memset(&mine, 0, sizeof(mine));
   _slot_bytes = (sizeof(double) * std::max<size_t>(_ghosts.size(), 1) + 255) / 256 * 256;
-  const size_t total = 2 * _slot_bytes + sizeof(std::uint32_t) * static_cast<size_t>(mpi_size);
+  // reverse_update lands in two more slots of _num_indices elements, with their own flags:
+  // [fwd slot 0 | fwd slot 1 | fwd flags | pad | rev slot 0 | rev slot 1 | rev flags]
+  _rev_slot_bytes = (sizeof(double) * std::max<size_t>(_num_indices, 1) + 255) / 256 * 256;
+  const size_t flag_bytes = (sizeof(std::uint32_t) * static_cast<size_t>(mpi_size) + 255) / 256 * 256;
+  _rev_base = 2 * _slot_bytes + flag_bytes;
+  const size_t total = _rev_base + 2 * _rev_slot_bytes + flag_bytes + 256; // + a scratch line for the probe
   void* stage = nullptr;
   if (ok && b200_ipc_alloc(&stage, total, mine.handle) != B200_OK)
     ok = 0;
-  // stream memory operations present?  (probe: a write to my own flag word)
-  if (ok && b200_stream_write_u32(gpu->comm_stream(), static_cast<char*>(stage) + 2 * _slot_bytes, 0u) != B200_OK)
+  // stream memory operations present?  Probe on a scratch word past every flag (the pad behind the
+  // reverse flags), and drain the stream before anybody can learn this buffer's address: a probe write
+  // still in flight must not be able to clobber an epoch a fast neighbour has already published.
+  if (ok
+      && (b200_stream_write_u32(gpu->comm_stream(), static_cast<char*>(stage) + total - sizeof(std::uint32_t), 0u) != B200_OK
+          || b200_stream_synchronize(gpu->comm_stream()) != B200_OK))
     ok = 0;
   _stage = static_cast<char*>(stage);
   mine.slot_bytes = static_cast<std::int64_t>(_slot_bytes);
+  mine.rev_base = static_cast<std::int64_t>(_rev_base);
+  mine.rev_slot_bytes = static_cast<std::int64_t>(_rev_slot_bytes);
   mine.ok = ok;
 
   std::vector<Card> cards(mpi_size);
@@ -163,12 +176,20 @@ void L2GMap::setup_peer_halo()
   for (int i = 0; i < nnbr; ++i)
     land_mine[_neighbours[i]] = _send_offset[i] - local_size;
   CHECK_MPI(MPI_Allgather(land_mine.data(), mpi_size, MPI_INT64_T, land_all.data(), mpi_size, MPI_INT64_T, _comm));
+  // reverse direction: rank q's ghost values that I own land at element _recv_offset[i] of my buffer
+  std::vector<std::int64_t> rland_mine(mpi_size, -1), rland_all(static_cast<size_t>(mpi_size) * mpi_size, -1);
+  for (int i = 0; i < nnbr; ++i)
+    rland_mine[_neighbours[i]] = _recv_offset[i];
+  CHECK_MPI(MPI_Allgather(rland_mine.data(), mpi_size, MPI_INT64_T, rland_all.data(), mpi_size, MPI_INT64_T, _comm));
   for (const Card& c : cards)
     ok = ok && c.ok != 0;
 
   _peer_stage.assign(nnbr, nullptr);
   _peer_slot_bytes.assign(nnbr, 0);
+  _peer_rev_base.assign(nnbr, 0);
+  _peer_rev_slot_bytes.assign(nnbr, 0);
   _land.assign(nnbr, -1);
+  _rev_land.assign(nnbr, -1);
   if (ok) {
     for (int i = 0; i < nnbr; ++i) {
       const int q = _neighbours[i];
@@ -179,7 +200,10 @@ void L2GMap::setup_peer_halo()
       }
       _peer_stage[i] = static_cast<char*>(p);
       _peer_slot_bytes[i] = static_cast<size_t>(cards[q].slot_bytes);
+      _peer_rev_base[i] = static_cast<size_t>(cards[q].rev_base);
+      _peer_rev_slot_bytes[i] = static_cast<size_t>(cards[q].rev_slot_bytes);
       _land[i] = land_all[static_cast<size_t>(q) * mpi_size + _mpi_rank];
+      _rev_land[i] = rland_all[static_cast<size_t>(q) * mpi_size + _mpi_rank];
     }
   }
   int all_ok = 0;
@@ -395,12 +419,37 @@ void L2GMap::reverse_update(T* vec_data) const
   if (nnbr == 0)
     return;
   const size_t need = sizeof(T) * static_cast<size_t>(std::max(_num_indices, 1));
-  if (_recv_buf == nullptr || _recv_buf_bytes < need) {
+  if (!_peer_ok && (_recv_buf == nullptr || _recv_buf_bytes < need)) {
     _exec->free(_recv_buf);
     _recv_buf = _exec->alloc<char>(need);
     _recv_buf_bytes = need;
   }
   detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  if (_peer_ok) {
+    // The forward peer halo run backwards: my ghost-tail slices go straight into their owners' reverse
+    // slots (copy engine over NVLink), a stream-ordered flag write publishes each, and the scatter-add
+    // reads the slot once every neighbour's flag has arrived.  Same two-slot argument as the forward
+    // exchange: a neighbour's push of epoch e+1 is stream-ordered after its wait for my epoch e.
+    void* stream = gpu->get_cuda_stream();
+    const std::uint32_t epoch = ++_rev_epoch;
+    const size_t slot = epoch & 1u;
+    for (int i = 0; i < nnbr; ++i) {
+      char* peer = _peer_stage[i] + _peer_rev_base[i];
+      if (_send_count[i] > 0)
+        detail::check(b200_memcpy_d2d_async(peer + slot * _peer_rev_slot_bytes[i] + sizeof(T) * static_cast<size_t>(_rev_land[i]),
+                                            vec_data + _send_offset[i], sizeof(T) * static_cast<size_t>(_send_count[i]),
+                                            stream),
+                      "peer reverse halo copy");
+      detail::check(b200_stream_write_u32(stream, peer + 2 * _peer_rev_slot_bytes[i] + sizeof(std::uint32_t) * _mpi_rank, epoch),
+                    "peer reverse halo flag");
+    }
+    char* mine = _stage + _rev_base;
+    for (int i = 0; i < nnbr; ++i)
+      detail::check(b200_stream_wait_u32_geq(stream, mine + 2 * _rev_slot_bytes + sizeof(std::uint32_t) * _neighbours[i], epoch),
+                    "peer reverse halo wait");
+    gpu->scatter_add_run(_num_indices, _indexbuf, reinterpret_cast<const T*>(mine + slot * _rev_slot_bytes), vec_data);
+    return;
+  }
   detail::check(b200_halo_exchange(gpu->nccl_comm(), nnbr, _neighbours.data(), vec_data, _send_count.data(),
                                    _send_offset.data(), _recv_buf, _recv_count.data(), _recv_offset.data(),
                                    static_cast<int>(sizeof(T)), gpu->get_cuda_stream()),

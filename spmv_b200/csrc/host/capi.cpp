@@ -52,6 +52,12 @@ Matrix<double>& as_mat(void* h)
     throw std::runtime_error("matrix handle is NULL");
   return *static_cast<Matrix<double>*>(h);
 }
+Matrix<float>& as_mat32(void* h)
+{
+  if (!h)
+    throw std::runtime_error("matrix handle is NULL");
+  return *static_cast<Matrix<float>*>(h);
+}
 CommunicationModel as_cm(int cm)
 {
   if (cm < 0 || cm > 7)
@@ -310,6 +316,63 @@ int spmvh_matrix_tune(void* mat, int which, int variant, int tile_bytes, int sta
                                      ctas_per_sm, nullptr),
                   "plan tune");
   });
+}
+
+// ---- fp32: the float instantiations of the same classes (Matrix.cpp:565, L2GMap.cpp:1001,1007,1012,
+// csr_kernels.cpp:62-63 in the reference) ----
+int spmvh_l2g_update_f32(void* map, float* d_vec)
+{
+  return guarded([&] { as_map(map).update(d_vec); });
+}
+int spmvh_l2g_update_finalise_f32(void* map, float* d_vec)
+{
+  return guarded([&] { as_map(map).update_finalise(d_vec); });
+}
+int spmvh_l2g_reverse_update_f32(void* map, float* d_vec)
+{
+  return guarded([&] { as_map(map).reverse_update(d_vec); });
+}
+int spmvh_matrix_create_f32(void** mat, void* exec, const int32_t* rowptr, const int32_t* colind, const float* values,
+                            int64_t nrows_local, int64_t ncols_local, const int64_t* row_ghosts,
+                            int64_t num_row_ghosts, const int64_t* col_ghosts, int64_t num_col_ghosts, int symmetric,
+                            int cm)
+{
+  return guarded([&] {
+    std::vector<std::int64_t> rg(row_ghosts, row_ghosts + num_row_ghosts);
+    std::vector<std::int64_t> cg(col_ghosts, col_ghosts + num_col_ghosts);
+    *mat = Matrix<float>::create_matrix(MPI_COMM_WORLD, as_exec(exec), rowptr, colind, values, nrows_local,
+                                        ncols_local, rg, cg, symmetric != 0, as_cm(cm));
+  });
+}
+int spmvh_matrix_destroy_f32(void* mat)
+{
+  return guarded([&] { delete static_cast<Matrix<float>*>(mat); });
+}
+int spmvh_matrix_info_f32(void* mat, int64_t out[8])
+{
+  return guarded([&] {
+    Matrix<float>& m = as_mat32(mat);
+    out[0] = m.rows();
+    out[1] = m.cols();
+    out[2] = m.non_zeros();
+    out[3] = m.symmetric() ? 1 : 0;
+    out[4] = static_cast<int64_t>(m.format_size());
+    out[5] = m.remote_block() ? 1 : 0;
+    out[6] = m.local_block() ? m.local_block()->non_zeros() : 0;
+    out[7] = m.remote_block() ? m.remote_block()->non_zeros() : 0;
+  });
+}
+int spmvh_matrix_col_map_f32(void* mat, void** map)
+{
+  return guarded([&] { *map = new MapPtr(std::const_pointer_cast<L2GMap>(as_mat32(mat).col_map())); });
+}
+int spmvh_matrix_mult_f32(void* mat, float* d_x, float* d_y)
+{
+  return guarded([&] { as_mat32(mat).mult(d_x, d_y); });
+}
+int spmvh_matrix_mult_host_f32(void* mat, const float* x_host, float* y_host)
+{
+  return guarded([&] { as_mat32(mat).mult_host(x_host, y_host); });
 }
 
 int spmvh_cg(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol, double* hist,

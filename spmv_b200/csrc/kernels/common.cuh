@@ -117,6 +117,33 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
                "r"(parity)
                : "memory");
 }
+// Non-blocking probe of the same phase (true: the phase with this parity has completed).
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity)
+{
+  uint32_t ok;
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+               "selp.u32 %0, 1, 0, p;\n"
+               "}"
+               : "=r"(ok)
+               : "r"(smem_u32(bar)), "r"(parity)
+               : "memory");
+  return ok != 0;
+}
+// Read-only gather that does not take an L1 line (random x gathers with no reuse inside the SM).
+__device__ __forceinline__ double ldg_na(const double* p)
+{
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ldg_na(const float* p)
+{
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
 // Global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16.
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
 {

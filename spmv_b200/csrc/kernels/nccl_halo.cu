@@ -156,15 +156,17 @@ int b200_halo_exchange(void* comm, int nnbr, const int32_t* nbr_rank, const void
   const char* sb = static_cast<const char*>(d_sendbuf);
   char* rb = static_cast<char*>(d_recvbuf);
   B200_NCCL(api.GroupStart());
-  for (int i = 0; i < nnbr; ++i) {
+  // an error inside the group must still close it: NCCL keeps the group open per thread otherwise
+  ncclResult_t bad = ncclSuccess;
+  for (int i = 0; i < nnbr && bad == ncclSuccess; ++i) {
     if (recv_cnt[i] > 0)
-      B200_NCCL(api.Recv(rb + (size_t)recv_off[i] * elem_bytes, (size_t)recv_cnt[i], dt,
-                         nbr_rank[i], c, st));
-    if (send_cnt[i] > 0)
-      B200_NCCL(api.Send(sb + (size_t)send_off[i] * elem_bytes, (size_t)send_cnt[i], dt,
-                         nbr_rank[i], c, st));
+      bad = api.Recv(rb + (size_t)recv_off[i] * elem_bytes, (size_t)recv_cnt[i], dt, nbr_rank[i], c, st);
+    if (bad == ncclSuccess && send_cnt[i] > 0)
+      bad = api.Send(sb + (size_t)send_off[i] * elem_bytes, (size_t)send_cnt[i], dt, nbr_rank[i], c, st);
   }
-  B200_NCCL(api.GroupEnd());
+  const ncclResult_t end = api.GroupEnd();
+  B200_NCCL(bad);
+  B200_NCCL(end);
   return B200_OK;
 }
 

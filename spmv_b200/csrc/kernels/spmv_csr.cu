@@ -54,6 +54,11 @@ constexpr int WALK_ROW16 = 0, WALK_STREAM = 1, WALK_ROW8 = 2, WALK_ROW4 = 3;
 constexpr int WALK_ROW8S = 4, WALK_ROW4S = 5;
 // segmented-scan walk for irregular rows (general storage): entry-parallel, warp-private, no CTA barrier
 constexpr int WALK_SEG = 6;
+// the same with L1::no_allocate x gathers
+constexpr int WALK_SEGNA = 7;
+__host__ __device__ constexpr bool walk_is_seg(int w) { return w == WALK_SEG || w == WALK_SEGNA; }
+// WALK_SEG: ints per tile in Plan::d_warp_rows (cw + 1 row offsets, padded to a 16-byte multiple for the bulk copy)
+__host__ __device__ constexpr int seg_stride(int cw) { return (cw + 1 + 3) & ~3; }
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
 constexpr int LONG_CAP = 256;  // long rows per tile (stage_bytes <= 96 KiB)
 constexpr int MAX_STAGE_BYTES = 96 * 1024;
@@ -80,7 +85,8 @@ struct SpmvArgs {
   T alpha;
   T beta;
   const int32_t* tile_meta;
-  const int32_t* warp_rows; // WALK_SEG: (CW+1) row offsets per tile, the consumer warps' segments
+  const int32_t* warp_rows; // WALK_SEG: seg_stride(CW) ints per tile, CW+1 row offsets: the consumer warps' segments
+  int32_t flags;            // bit 0: WALK_SEG matrix stream with the evict_first L2 policy
   int32_t tile0;     // first tile of this launch (tile sub-ranges: pipelined host-vector SpMV)
   int32_t num_tiles; // end of the tile range
   int32_t stage_bytes;
@@ -301,15 +307,15 @@ __device__ __forceinline__ dd walk_stream(const SpmvArgs<T>& a, unsigned char* s
     for (int u = 0; u < U; ++u) {
       const int j = j0 + u * nthreads;
       const bool ok = j < n;
-      c[u] = ok ? sc[j] : r0;
+      c[u] = ok ? sc[j] : (EXT ? r0 : 0);
       v[u] = ok ? sv[j] : T(0);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (EXT && (unsigned)(c[u] - r0) < (unsigned)nrows)
         xv[u] = sx[c[u] - r0];
-      else
-        xv[u] = __ldg(a.x + c[u]);
+      else // padded slots gather nothing: a block may have more rows than columns, x[r0] need not exist
+        xv[u] = (j0 + u * nthreads < n) ? __ldg(a.x + c[u]) : T(0);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -452,73 +458,153 @@ __device__ __forceinline__ dd walk_direct_cta(const SpmvArgs<T>& a, int r0, int 
 }
 
 // ---------------------------------------------------------------------------
-// Warp-private stream walk (WALK_SEG; general storage, irregular row lengths).
-// The stream walk's two phases -- products by entry, sums by row -- but each consumer
-// warp owns a SEGMENT of the tile: the rows that start in its equal share of the
-// tile's entries, cut at plan time (plan_warp_rows_kernel; a.warp_rows holds CW+1 row
-// offsets per tile).  Phase 1, lanes over the segment's entries: product with the
-// gathered x, written back over the staged value, four gathers in flight per lane.
-// Phase 2, lanes over its rows: left-to-right sum of the products (the reference's
-// order, so rows <= 32 entries stay bit-identical); longer rows by the whole warp.
-// Only __syncwarp between the phases: no warp waits for another until the stage is
-// released, so with 3 stages a warp that drew a 1000-entry row does not hold up the
-// CTA (the two CTA-wide barriers per tile were 11 of 30 stall cycles per issue in
-// the stream walk on the power-law matrix, profiles/r01_powerlaw_walks.md).
+// Warp-private, software-pipelined stream walk (WALK_SEG / WALK_SEGNA; general storage,
+// irregular row lengths).  The stream walk's two phases -- products by entry, sums by
+// row -- but each consumer warp owns a SEGMENT of every tile: the rows that start in its
+// equal share of the tile's entries, cut at plan time (plan_warp_rows_kernel; the
+// producer stages the tile's cw + 1 row offsets next to the rowptr slice).  No warp ever
+// waits for another one: the only synchronisation is the full / empty mbarrier pair of
+// the stage, on which every warp arrives for itself.  (The two CTA-wide barriers per tile
+// of walk_stream were 11 of 30 stall cycles per issue on the power-law matrix,
+// profiles/r01_powerlaw_stream_ncu_summary.txt.)
+//   open   : wait for the tile, read this warp's segment, ISSUE the x gathers of its first
+//            32*SEG_U entries into registers;
+//   finish : products val*x written back over the staged values (rest of an over-long
+//            segment gathered here, four in flight per lane);
+//   sums   : lanes over the segment's rows, left-to-right sums of the products in chunks of
+//            eight loads followed by eight dependent adds (the reference's order,
+//            csr_kernels.cpp:45-47: rows <= 32 entries stay bit-identical); longer rows by
+//            the whole warp.
+// The loop runs `open` of tile i+1 BEFORE `sums` of tile i whenever that tile has already
+// landed (mbarrier.test_wait), so the L2 latency of the gathers hides behind the
+// shared-memory sums instead of adding to them.
 // ---------------------------------------------------------------------------
-template <typename T, bool DOT>
-__device__ __forceinline__ dd walk_seg(const SpmvArgs<T>& a, unsigned char* stage, const StageMeta* m, int ka,
-                                       int kb, int lane)
-{
-  constexpr int U = 4;
-  constexpr unsigned FULL = 0xffffffffu;
-  const int r0 = m->r0, nrows = m->nstaged, lo = m->lo, hi = m->hi;
-  const TileLayout<T, LAY_PLAIN> L(r0, nrows, lo, hi);
-  T* sv = reinterpret_cast<T*>(stage) + (lo - L.lo_v);                       // sv[j - lo]
-  const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c); // sc[j - lo]
-  const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r);
-  dd dot = {0.0, 0.0};
-  ka = min(ka, nrows); // the producer may have staged a prefix of the tile's rows only
-  kb = min(kb, nrows);
-  if (ka >= kb)
-    return dot;
-  const int ea = sr[ka] - lo, eb = sr[kb] - lo;
+template <typename T>
+struct SegU {
+  static constexpr int value = sizeof(T) == 8 ? 4 : 8; // gathers per lane carried across the previous tile's sums
+};
 
-  for (int j0 = ea + lane; j0 < eb; j0 += 32 * U) {
-    int c[U];
-    T v[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int j = j0 + u * 32;
-      const bool ok = j < eb;
-      c[u] = ok ? sc[j] : 0;
-      v[u] = ok ? sv[j] : T(0);
+// Shared-memory byte offsets (32-bit: two tiles' worth of these live in registers per thread)
+template <typename T>
+struct SegTile {
+  int sv; // byte offset of the staged value of entry `lo` (overwritten by the products)
+  int sc; // ... of its column index
+  int sr; // ... of rowptr[r0]
+  int r0, lo, ns, nrows;
+  int ka, kb; // this warp's rows of the tile
+  int ea, eb; // ... and their entries, relative to lo
+};
+
+template <typename T, bool NA>
+__device__ __forceinline__ T seg_gather(const T* p)
+{
+  if constexpr (NA)
+    return ldg_na(p);
+  else
+    return __ldg(p);
+}
+
+// This warp's view of the tile in stage s (the stage must have landed).
+template <typename T>
+__device__ __forceinline__ SegTile<T> seg_tile(const SpmvArgs<T>& a, const unsigned char* smem, const StageMeta* meta,
+                                               int s, int warp)
+{
+  const StageMeta* m = meta + s;
+  const int base = s * a.stage_bytes;
+  SegTile<T> t;
+  const int r0 = m->r0, ns = m->nstaged, lo = m->lo, hi = m->hi;
+  t.r0 = r0;
+  t.lo = lo;
+  t.ns = ns;
+  t.nrows = m->nrows;
+  t.sv = t.sc = t.sr = base;
+  t.ka = t.kb = t.ea = t.eb = 0;
+  if (ns > 0) {
+    const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
+    t.sv = base + (lo - L.lo_v) * (int)sizeof(T);
+    t.sc = base + L.off_c() + (lo - L.lo_c) * 4;
+    t.sr = base + L.off_r() + (r0 - L.lo_r) * 4;
+    const int* wr = reinterpret_cast<const int*>(smem + base + L.off_d());
+    const int* sr = reinterpret_cast<const int*>(smem + t.sr);
+    t.ka = min(wr[warp], ns); // the producer may have staged a prefix of the tile's rows only
+    t.kb = min(wr[warp + 1], ns);
+    if (t.ka < t.kb) {
+      t.ea = sr[t.ka] - lo;
+      t.eb = sr[t.kb] - lo;
     }
+  }
+  return t;
+}
+
+template <typename T, bool NA>
+__device__ __forceinline__ void seg_issue(const SpmvArgs<T>& a, const unsigned char* smem, const SegTile<T>& t, int lane,
+                                          T (&xv)[SegU<T>::value])
+{
+  const int* sc = reinterpret_cast<const int*>(smem + t.sc);
+#pragma unroll
+  for (int u = 0; u < SegU<T>::value; ++u) {
+    const int j = t.ea + lane + 32 * u;
+    xv[u] = j < t.eb ? seg_gather<T, NA>(a.x + sc[j]) : T(0);
+  }
+}
+
+template <typename T, bool NA>
+__device__ __forceinline__ void seg_finish(const SpmvArgs<T>& a, unsigned char* smem, const SegTile<T>& t,
+                                           const T (&xv)[SegU<T>::value], int lane)
+{
+  T* sv = reinterpret_cast<T*>(smem + t.sv);
+  const int* sc = reinterpret_cast<const int*>(smem + t.sc);
+#pragma unroll
+  for (int u = 0; u < SegU<T>::value; ++u) {
+    const int j = t.ea + lane + 32 * u;
+    if (j < t.eb)
+      sv[j] = mul_rn(sv[j], xv[u]);
+  }
+  constexpr int U = 4;
+  for (int j0 = t.ea + 32 * SegU<T>::value + lane; j0 < t.eb; j0 += 32 * U) {
+    T w[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      if (j0 + u * 32 < eb)
-        v[u] = mul_rn(v[u], __ldg(a.x + c[u]));
+      w[u] = j0 + 32 * u < t.eb ? seg_gather<T, NA>(a.x + sc[j0 + 32 * u]) : T(0);
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      if (j0 + u * 32 < eb)
-        sv[j0 + u * 32] = v[u];
+      if (j0 + 32 * u < t.eb)
+        sv[j0 + 32 * u] = mul_rn(sv[j0 + 32 * u], w[u]);
   }
   __syncwarp();
+}
 
-  for (int k0 = ka; k0 < kb; k0 += 32) {
+template <typename T, bool DOT>
+__device__ __forceinline__ void seg_sums(const SpmvArgs<T>& a, const unsigned char* smem, const SegTile<T>& t, int lane,
+                                         dd& dot)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int C = 8;
+  const T* sv = reinterpret_cast<const T*>(smem + t.sv);
+  const int* sr = reinterpret_cast<const int*>(smem + t.sr);
+  for (int k0 = t.ka; k0 < t.kb; k0 += 32) {
     const int k = k0 + lane;
     int rs = 0, re = 0;
-    if (k < kb) {
-      rs = sr[k] - lo;
-      re = sr[k + 1] - lo;
+    if (k < t.kb) {
+      rs = sr[k] - t.lo;
+      re = sr[k + 1] - t.lo;
     }
     const bool is_long = re - rs > SHORT_ROW;
-    if (k < kb && !is_long) {
+    if (k < t.kb && !is_long) {
       T sum = T(0);
-      for (int j = rs; j < re; ++j)
-        sum = add_rn(sum, sv[j]);
-      const T out = store_row<T, false>(a, r0 + k, sum);
+      for (int b = rs; b < re; b += C) {
+        T pv[C];
+#pragma unroll
+        for (int u = 0; u < C; ++u)
+          pv[u] = b + u < re ? sv[b + u] : T(0);
+#pragma unroll
+        for (int u = 0; u < C; ++u)
+          if (b + u < re)
+            sum = add_rn(sum, pv[u]);
+      }
+      const T out = store_row<T, false>(a, t.r0 + k, sum);
       if (DOT)
-        dd_add_prod(dot, (double)__ldg(a.x + r0 + k), (double)out);
+        dd_add_prod(dot, (double)__ldg(a.x + t.r0 + k), (double)out);
     }
     unsigned todo = __ballot_sync(FULL, is_long);
     while (todo) {
@@ -530,11 +616,65 @@ __device__ __forceinline__ dd walk_seg(const SpmvArgs<T>& a, unsigned char* stag
         part += sv[j];
       part = warp_sum(part);
       if (lane == 0) {
-        const T out = store_row<T, false>(a, r0 + k0 + src, part);
+        const T out = store_row<T, false>(a, t.r0 + k0 + src, part);
         if (DOT)
-          dd_add_prod(dot, (double)__ldg(a.x + r0 + k0 + src), (double)out);
+          dd_add_prod(dot, (double)__ldg(a.x + t.r0 + k0 + src), (double)out);
       }
     }
+  }
+}
+
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+template <typename T, bool DOT, int CW, bool NA>
+__device__ __forceinline__ dd seg_consumer(const SpmvArgs<T>& a, unsigned char* smem, StageMeta* meta, uint64_t* full,
+                                           uint64_t* empty, int my_tiles, int warp, int lane, double* s_warp)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int U = SegU<T>::value;
+  const int stages = a.stages;
+  dd dot = {0.0, 0.0};
+  if (my_tiles <= 0)
+    return dot;
+  T xv[U];
+  int s = 0, use = 0;
+  mbar_wait(full, 0);
+  SegTile<T> cur = seg_tile<T>(a, smem, meta, 0, warp);
+  seg_issue<T, NA>(a, smem, cur, lane, xv);
+  for (int it = 0; it < my_tiles; ++it) {
+    seg_finish<T, NA>(a, smem, cur, xv, lane);
+    const int s1 = s + 1 == stages ? 0 : s + 1;
+    const int use1 = use + (s1 == 0);
+    const bool more = it + 1 < my_tiles;
+    bool early = false;
+    if (more) {
+      // has the next tile landed already?  then its gathers go out now and fly during the sums
+      early = __shfl_sync(FULL, (int)mbar_test(full + s1, use1 & 1), 0) != 0;
+      if (early) {
+        const SegTile<T> nxt = seg_tile<T>(a, smem, meta, s1, warp);
+        seg_issue<T, NA>(a, smem, nxt, lane, xv);
+      }
+    }
+    seg_sums<T, DOT>(a, smem, cur, lane, dot);
+    if (cur.ns < cur.nrows)
+      dot = dd_merge(dot, walk_direct_cta<T, false, DOT>(a, cur.r0 + cur.ns, cur.nrows - cur.ns, threadIdx.x, CW * 32,
+                                                         warp, CW, lane, 1, s_warp));
+    fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(empty + s);
+    if (more) {
+      if (!early)
+        mbar_wait(full + s1, use1 & 1);
+      cur = seg_tile<T>(a, smem, meta, s1, warp); // (recomputed rather than carried: registers)
+      if (!early)
+        seg_issue<T, NA>(a, smem, cur, lane, xv);
+    }
+    s = s1;
+    use = use1;
   }
   return dot;
 }
@@ -544,15 +684,19 @@ __device__ __forceinline__ dd walk_seg(const SpmvArgs<T>& a, unsigned char* stag
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
 //   WALK_ROW16/8/4: one thread per row (chunked gathers);  WALK_STREAM: two-phase stream walk.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ void fence_proxy_async_smem()
+// resident CTAs per SM the register allocation must allow (only the warp-private walk asks: its two
+// tiles in flight per warp would otherwise take ~94 registers and a single CTA per SM)
+__host__ __device__ constexpr int pipe_min_ctas(bool sym, int walk, int cw)
 {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  return (!sym && walk_is_seg(walk)) ? (cw == 16 ? 2 : 3) : 1;
 }
 
 template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
-__global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
+__global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
-  constexpr int LAY = SYM ? ((WALK == WALK_STREAM || WALK == WALK_SEG) ? LAY_DXP : LAY_DX) : LAY_PLAIN;
+  constexpr bool SEGW = !SYM && walk_is_seg(WALK); // warp-private pipelined walk (general storage only)
+  constexpr int WR_BYTES = SEGW ? seg_stride(CW) * 4 : 0;
+  constexpr int LAY = SYM ? ((WALK == WALK_STREAM || walk_is_seg(WALK)) ? LAY_DXP : LAY_DX) : LAY_PLAIN;
   constexpr int CHUNK = (WALK == WALK_ROW4 || WALK == WALK_ROW4S) ? 4 : ((WALK == WALK_ROW8 || WALK == WALK_ROW8S) ? 8 : 16);
   constexpr bool SINGLE = WALK == WALK_ROW4S || WALK == WALK_ROW8S;
   extern __shared__ __align__(128) unsigned char smem[];
@@ -578,24 +722,48 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
 
   if (warp == CW) {
     if (lane == 0) {
-      const uint64_t pol_stream = SYM ? l2_policy_evict_first() : 0ull;
+      const uint64_t pol_stream = (SYM || SEGW) ? l2_policy_evict_first() : 0ull;
+      const bool hint = SYM || (SEGW && (a.flags & 1));
       auto stream_g2s = [&](void* d, const void* g, uint32_t bytes, uint64_t* bar) {
-        if constexpr (SYM)
-          bulk_g2s_hint(d, g, bytes, bar, pol_stream);
-        else
+        if constexpr (SYM || SEGW) {
+          if (hint)
+            bulk_g2s_hint(d, g, bytes, bar, pol_stream);
+          else
+            bulk_g2s(d, g, bytes, bar);
+        } else {
           bulk_g2s(d, g, bytes, bar);
+        }
       };
+      const int2* tmeta = reinterpret_cast<const int2*>(a.tile_meta);
+      // SEGW: the tile table entry of the NEXT tile is fetched before the wait for a free stage, so the
+      // producer's chain per tile is not table load -> wait -> issue (~1.4 us per tile and CTA,
+      // profiles/r01_powerlaw_walks.md) but max(table load, wait) -> issue
+      int2 n0 = make_int2(0, 0), n1 = make_int2(0, 0);
+      if (SEGW && my_tiles > 0) {
+        n0 = __ldg(tmeta + a.tile0 + blockIdx.x);
+        n1 = __ldg(tmeta + a.tile0 + blockIdx.x + 1);
+      }
       for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
+        const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
+        int2 t0, t1;
+        if constexpr (SEGW) {
+          t0 = n0, t1 = n1;
+          if (it + 1 < my_tiles) {
+            n0 = __ldg(tmeta + tile + gridDim.x);
+            n1 = __ldg(tmeta + tile + gridDim.x + 1);
+          }
+        }
         if (use > 0)
           mbar_wait(empty + s, (use - 1) & 1);
-        const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
-        const int2 t0 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile);
-        const int2 t1 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile + 1);
+        if constexpr (!SEGW) {
+          t0 = __ldg(tmeta + tile);
+          t1 = __ldg(tmeta + tile + 1);
+        }
         const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x;
         // Stage the longest prefix of rows that fits: a tile overshoots its byte
         // budget by at most its last row, so this drops one (long) row at most.
         int ns = nrows, hi = t1.y;
-        while (ns > 0 && !tile_fits<T, LAY>(r0, ns, lo, hi, sb)) {
+        while (ns > 0 && !tile_fits<T, LAY>(r0, ns, lo, hi, sb - WR_BYTES)) {
           --ns;
           hi = __ldg(a.rowptr + r0 + ns);
         }
@@ -609,7 +777,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
         if (ns > 0) {
           const TileLayout<T, LAY> L(r0, ns, lo, hi);
           unsigned char* dst = smem + (size_t)s * sb;
-          mbar_arrive_expect_tx(full + s, (uint32_t)L.loaded());
+          mbar_arrive_expect_tx(full + s, (uint32_t)(L.loaded() + WR_BYTES));
           // Symmetric storage: the matrix is read once per SpMV, while the y lines are touched several
           // times (zero-fill, the row's own add, the adds from the rows that list it).  evict_first on
           // the matrix stream keeps it from displacing them in L2: sym 7-pt 0.220 -> 0.213 ms, sym 27-pt
@@ -624,6 +792,8 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
             stream_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
             bulk_g2s(dst + L.off_x(), a.x + L.lo_d, L.bytes_d, full + s);
           }
+          if constexpr (SEGW) // the consumer warps' row segments of this tile, next to the rowptr slice
+            bulk_g2s(dst + L.off_d(), a.warp_rows + (size_t)tile * seg_stride(CW), WR_BYTES, full + s);
         } else {
           mbar_arrive(full + s);
         }
@@ -637,7 +807,10 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
   // 0.85 -> 1.04 ms) with the incremental stage counters and the CTA-wide direct walk in the loop
   // body, and the 8-entry general walk ~2% better (7-point: 0.257 -> 0.251 ms), A/B-measured in
   // profiles/r01_powerlaw_walks.md; the irregular walks need the CTA-wide direct walk.
-  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || WALK == WALK_SEG || (!SYM && CHUNK == 8);
+  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || walk_is_seg(WALK) || (!SYM && CHUNK == 8);
+  if constexpr (SEGW) {
+    dot = seg_consumer<T, DOT, CW, WALK == WALK_SEGNA>(a, smem, meta, full, empty, my_tiles, warp, lane, s_warp);
+  } else
   for (int it = 0, cs = 0, cu = 0; it < my_tiles; ++it) {
     int s, use;
     if constexpr (CTA_DIRECT) {
@@ -647,20 +820,11 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
     } else {
       s = it % stages, use = it / stages;
     }
-    int seg_a = 0, seg_b = 0; // this warp's rows of the tile (their load overlaps the wait)
-    if (WALK == WALK_SEG && !SYM) {
-      const int32_t* wr = a.warp_rows + (size_t)(a.tile0 + blockIdx.x + it * gridDim.x) * (CW + 1) + warp;
-      seg_a = __ldg(wr);
-      seg_b = __ldg(wr + 1);
-    }
     mbar_wait(full + s, use & 1);
     StageMeta* m = meta + s;
     const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
     if (ns > 0) {
-      if (WALK == WALK_SEG && !SYM) {
-        dot = dd_merge(dot, walk_seg<T, DOT>(a, smem + (size_t)s * sb, m, seg_a, seg_b, lane));
-        fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
-      } else if (WALK == WALK_STREAM || WALK == WALK_SEG) {
+      if (WALK == WALK_STREAM || walk_is_seg(WALK)) {
         dot = dd_merge(dot, walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32,
                                                            warp, CW, lane, 1));
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
@@ -874,12 +1038,16 @@ __global__ void plan_tiles_kernel(const int32_t* __restrict__ rowptr, int rows, 
 // out[t*(cw+1) + w] = first row of tile t (as an offset from the tile's first row) that starts at
 // or after entry lo + n*w/cw; segment w = rows [out[w], out[w+1]).
 __global__ void plan_warp_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ meta,
-                                      int num_tiles, int cw, int32_t* __restrict__ out)
+                                      int num_tiles, int cw, int stride, int32_t* __restrict__ out)
 {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (long long)num_tiles * (cw + 1))
+  if (i >= (long long)num_tiles * stride)
     return;
-  const int t = (int)(i / (cw + 1)), w = (int)(i % (cw + 1));
+  const int t = (int)(i / stride), w = (int)(i % stride);
+  if (w > cw) { // padding up to the 16-byte multiple the bulk copy moves
+    out[i] = 0;
+    return;
+  }
   const int r0 = meta[2 * t], lo = meta[2 * t + 1], r1 = meta[2 * t + 2], hi = meta[2 * t + 3];
   const int target = lo + (int)((long long)(hi - lo) * w / cw);
   int x0 = r0, x1 = r1; // first row in [r0, r1] with rowptr[row] >= target
@@ -972,7 +1140,7 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   p->w_row = 4;
   if (p->symmetric && p->variant == 0) {
     p->w_row = 20; // rowptr + diagonal + x
-    if (p->walk == WALK_STREAM || p->walk == WALK_SEG)
+    if (p->walk == WALK_STREAM || walk_is_seg(p->walk))
       p->w_entry = 20; // value + column + product
   }
   const long long total = (long long)p->w_entry * p->nnz + (long long)p->w_row * p->rows;
@@ -985,11 +1153,12 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   plan_tiles_kernel<<<blocks, threads, 0, st>>>(d_rowptr, p->rows, p->nnz, p->num_tiles,
                                                 p->tile_bytes, p->w_entry, p->w_row, p->d_tile_meta);
   B200_LAUNCH_CHECK();
-  if (p->walk == WALK_SEG && !p->symmetric && p->variant == 0) {
-    const long long n = nt * (p->consumer_warps + 1);
+  if (walk_is_seg(p->walk) && !p->symmetric && p->variant == 0) {
+    const int stride = seg_stride(p->consumer_warps);
+    const long long n = nt * stride;
     B200_CUDA(cudaMalloc(&p->d_warp_rows, sizeof(int32_t) * (size_t)n));
     plan_warp_rows_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, st>>>(
-        d_rowptr, p->d_tile_meta, p->num_tiles, p->consumer_warps, p->d_warp_rows);
+        d_rowptr, p->d_tile_meta, p->num_tiles, p->consumer_warps, stride, p->d_warp_rows);
     B200_LAUNCH_CHECK();
   }
   return B200_OK;
@@ -1040,8 +1209,11 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
       *tile_bytes = 24 * 1024, *cw = 8, *ctas = 4;
     break;
   case WALK_STREAM:
-  case WALK_SEG:
     *tile_bytes = 24 * 1024, *cw = 16, *ctas = 2;
+    break;
+  case WALK_SEG:
+  case WALK_SEGNA:
+    *tile_bytes = 16 * 1024, *stages = 3, *cw = 16, *ctas = 2;
     break;
   default:
     *tile_bytes = 48 * 1024, *cw = 8, *ctas = 2;
@@ -1051,15 +1223,15 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
 // b200_csr_plan_tune's variant -> forced walk (-1: chosen from the histogram)
 static int walk_of_variant(int variant)
 {
-  return variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
+  return variant == 7 ? WALK_SEGNA : variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
 }
 
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant >= 0 && variant <= 6, "variant must be 0..6");
+  B200_REQUIRE(variant >= 0 && variant <= 7, "variant must be 0..7");
   // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
   // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4;
-  // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM)
+  // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM); 7: WALK_SEGNA
   p->walk_forced = walk_of_variant(variant);
   if (variant >= 2)
     variant = 0;
@@ -1129,10 +1301,15 @@ static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st
   case WALK_STREAM:
     return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
   case WALK_SEG:
-    if constexpr (SYM) // the scan walk is general-storage only
+    if constexpr (SYM) // the warp-private walk is general-storage only
       return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
     else
       return launch_pipe_cw<T, SYM, DOT, false, WALK_SEG>(p, a, st);
+  case WALK_SEGNA:
+    if constexpr (SYM)
+      return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
+    else
+      return launch_pipe_cw<T, SYM, DOT, false, WALK_SEGNA>(p, a, st);
   case WALK_ROW8:
     if (p.max_row_len <= 8)
       return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW8S>(p, a, st);
@@ -1251,6 +1428,10 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.beta = beta;
   a.tile_meta = p.d_tile_meta;
   a.warp_rows = p.d_warp_rows;
+  {
+    static const int seg_ef = env_int("B200_SPMV_SEG_EVICT_FIRST", 0);
+    a.flags = seg_ef ? 1 : 0;
+  }
   a.tile0 = ranged ? tile_begin : 0;
   a.num_tiles = ranged ? tile_end : p.num_tiles;
   a.stage_bytes = p.stage_bytes;

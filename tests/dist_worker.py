@@ -208,6 +208,74 @@ def main():
                 check(all(torch.equal(g, gathered[0]) for g in gathered), f"allreduce_sum nccl={use_nccl}: ranks disagree")
         A.close()
 
+    # L2GMap::reverse_update (L2GMap.cpp:908-923): ghost values travel back to their owners and are added
+    # onto vec[indexbuf[k]].  Expected values from the message-free restatement (oracle/plan.py, itself
+    # pinned to the reference's reverse_update_collective in tests/test_oracle.py), three calls in a row (the
+    # peer staging slots alternate by epoch), peer-memory exchange and the NCCL fallback, fp64 and fp32.
+    if mode == "gpu":
+        from oracle import plan as OP
+        for kind, n in (("fixture", None), ("lap7", (7, 6, 8)), ("powerlaw", 4000)):
+            N, rows = cases.make_problem(kind, n)
+            inps = [cases.local_inputs(rows, N, r, size) for r in range(size)]
+            plans = OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps])
+            for halo in ("peer", "nccl"):
+                if halo == "nccl":
+                    os.environ["B200_HALO"] = "nccl"
+                inp = inps[rank]
+                A = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                             inp["ncols_local"], [], inp["col_ghosts"], False, api.COLLECTIVE_BLOCKING)
+                os.environ.pop("B200_HALO", None)
+                cmap = A.col_map()
+                check(cases.same_plan(cmap.plan(), plans[rank]), f"reverse_update {kind}: plan differs from the restatement")
+                for dt, tol in ((torch.float64, 1e-14), (torch.float32, 1e-6)):
+                    npdt = np.float64 if dt == torch.float64 else np.float32
+                    vecs = [np.random.default_rng(77 + r).standard_normal(p["local_size"] + p["num_ghosts"]).astype(npdt)
+                            for r, p in enumerate(plans)]
+                    x = torch.from_numpy(vecs[rank].copy()).to(dev)
+                    for rep in range(3):
+                        cmap.reverse_update(x)
+                        OP.reverse_update(plans, vecs)
+                        for v, p in zip(vecs, plans):  # the tail is not changed by the call; refresh it so every
+                            v[p["local_size"]:] += 1     # epoch moves different numbers
+                        x[plans[rank]["local_size"]:] += 1
+                    ex.synchronize()
+                    err = rel_l2(x.cpu().numpy().astype(np.float64), vecs[rank].astype(np.float64))
+                    check(err < tol, f"reverse_update {kind} halo={halo} {dt}: rel err {err}")
+                    # forward update of the same dtype: ghosts are copies, bit for bit
+                    vecs2 = [np.random.default_rng(99 + r).standard_normal(p["local_size"] + p["num_ghosts"]).astype(npdt)
+                             for r, p in enumerate(plans)]
+                    x2 = torch.from_numpy(vecs2[rank].copy()).to(dev)
+                    cmap.update(x2)
+                    cmap.update_finalise(x2)
+                    OP.update(plans, vecs2)
+                    ex.synchronize()
+                    check(np.array_equal(x2.cpu().numpy(), vecs2[rank]), f"update {kind} halo={halo} {dt}: ghosts differ")
+                A.close()
+
+    # fp32 through the API (Matrix<float>::create_matrix -> L2GMap::update<float> -> Matrix<float>::mult)
+    if mode == "gpu":
+        from oracle import kernels as OKf
+        for kind, n, sym, cm in (("fixture", None, False, api.P2P_BLOCKING), ("fixture", None, True, api.COLLECTIVE_BLOCKING),
+                                 ("lap7", (7, 6, 8), True, api.P2P_NONBLOCKING), ("lap27", (6, 5, 8), False, api.P2P_NONBLOCKING),
+                                 ("lap27", (6, 5, 8), False, api.COLLECTIVE_BLOCKING)):
+            N, rows = cases.make_problem(kind, n)
+            inp = cases.local_inputs(rows, N, rank, size)
+            A = api.MatrixF32.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"].astype(np.float32),
+                                            inp["nrows_local"], inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
+            cmap = A.col_map()
+            xg = (synth.bump_vector(N, 0, N) + 0.1).astype(np.float32)
+            x = torch.zeros(cmap.local_size() + cmap.num_ghosts(), dtype=torch.float32, device=dev)
+            x[: inp["nrows_local"]] = torch.from_numpy(xg[inp["r0"]:inp["r1"]]).to(dev)
+            y = torch.full((inp["nrows_local"],), float("nan"), dtype=torch.float32, device=dev)
+            cmap.update(x)
+            A.mult(x, y)
+            ex.synchronize()
+            rp, col, val = rows(0, N)  # the fp32 oracle on the global operator, this rank's rows
+            want = OKf.spmv(rp.astype(np.int32), col.astype(np.int32), val.astype(np.float32), xg)[inp["r0"]:inp["r1"]]
+            err = rel_l2(y.cpu().numpy().astype(np.float64), want.astype(np.float64))
+            check(err < 2e-6, f"fp32 {kind} sym={sym} cm={cm} size={size}: rel err {err}")
+            A.close()
+
     # mult_host on slabs big enough for several chunks and distinct edge pages
     if mode == "gpu":
         for st, sym, cm in ((7, True, api.P2P_NONBLOCKING), (27, False, api.P2P_NONBLOCKING),

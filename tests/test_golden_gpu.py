@@ -148,3 +148,46 @@ def test_mult_host_pageable_and_tiny(ex):
         A.mult_host(np.ascontiguousarray(g["x"]), y)
         assert rel_l2(y, g["y_general"]) < TOL_Y
         A.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# CG trajectory at a size where rounding has room to show: 27-point 64^3 (262 144 rows), 120
+# iterations with rtol out of reach, against the reference's own cg.cpp run here through oracle/_ref
+# (tier 2, one thread-rank) and against the restated CG's residual history.  General storage with
+# stencil rows: iteration count, x and every ||r_k|| bit-identical.
+# ---------------------------------------------------------------------------------------------
+def test_cg_bit_identical_to_reference_64cubed(ex):
+    from oracle import cg as OCG
+    from oracle import kernels as OK
+    from oracle import ref_api as R
+    from spmv_b200 import synth
+    n1, kmax = 64, 120
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    rp32, c32 = rp.astype(np.int32), col.astype(np.int32)
+    mult = lambda p: OK.spmv(rp32, c32, val, p)  # noqa: E731
+    b_h = mult(np.ones(N))
+    it_o, x_o, hist_o = OCG.cg(mult, b_h, kmax, 1e-30)
+    assert it_o == kmax
+    if R.available():  # the reference's own loop (cg.cpp:21-98) on its own Matrix
+        res = {}
+
+        def body(rank):
+            M = R.RefMatrix.create_matrix(rp32, c32, val, N, N, [], [], False, 2)
+            res["cg"] = M.cg(b_h, kmax, 1e-30)
+            M.close()
+
+        R.run_ranks(1, body)
+        assert res["cg"][0] == it_o and np.array_equal(res["cg"][1], x_o)  # restatement == reference
+    A = api.Matrix.create_matrix(ex, rp32, c32, val, N, N, [], [], False, api.P2P_BLOCKING)
+    b = torch.from_numpy(b_h).cuda()
+    x = torch.zeros(N, dtype=torch.float64, device="cuda")
+    it, hist = api.cg(ex, A, b, x, kmax, 1e-30, history=True)
+    assert it == it_o
+    assert np.array_equal(hist, hist_o)
+    assert np.array_equal(x.cpu().numpy(), x_o)
+    # and the solve to the BASELINE tolerance stops at the same iteration
+    it8, hist8 = api.cg(ex, A, b, x, 5000, 1e-8, history=True)
+    it8_o, x8_o, hist8_o = OCG.cg(mult, b_h, 5000, 1e-8)
+    assert it8 == it8_o and np.array_equal(hist8, hist8_o) and np.array_equal(x.cpu().numpy(), x8_o)
+    A.close()

@@ -208,3 +208,118 @@ def test_powerlaw_petsc_file_is_the_same_bytes(tmp_path):
         assert fa.read() == fb.read()
     with pytest.raises(RuntimeError):
         api.write_powerlaw_petsc(str(tmp_path / "no_such_dir" / "c.petsc"), 100)
+
+
+# ---------------------------------------------------------------------------------------------
+# The halo plan, pinned WITHOUT any message passing (oracle/plan.py): tier 2 and the product's
+# host layer both link the thread-rank MPI shim, so a bug in the shim's neighbour-collective
+# ordering would cancel out of every "bit-exact vs reference" comparison between those two
+# (VERDICT r1, weak #3).  Three independent pins: a hand-derived 3-rank example, the message-free
+# restatement, and the golden file (output of the reference's own L2GMap.cpp).
+# ---------------------------------------------------------------------------------------------
+# 5x5 fixture (tests/test_spmv.cpp:56-63) at 3 ranks, derived by hand from SURVEY App. A:
+# ranges [0,2,4,5]; rank 0 rows 0-1 touch columns {0,1,3}; rank 1 rows 2-3 touch {2,3,4},{0,1,2,3};
+# rank 2 row 4 touches {2,4}.
+HAND_3RANK = [
+    dict(ghosts=[3], neighbours=[1], send_count=[1], recv_count=[2], send_offset=[2, 3], recv_offset=[0, 2],
+         indexbuf=[0, 1]),
+    dict(ghosts=[0, 1, 4], neighbours=[0, 2], send_count=[2, 1], recv_count=[1, 1], send_offset=[2, 4, 5],
+         recv_offset=[0, 1, 2], indexbuf=[1, 0]),
+    dict(ghosts=[2], neighbours=[1], send_count=[1], recv_count=[1], send_offset=[1, 2], recv_offset=[0, 1],
+         indexbuf=[0]),
+]
+
+
+def _global_plans(kind, n, size):
+    from oracle import plan as OP
+    from tests import cases
+    N, rows = cases.make_problem(kind, n)
+    inps = [cases.local_inputs(rows, N, r, size) for r in range(size)]
+    return OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps]), inps, (N, rows)
+
+
+def test_plan_hand_derived_three_ranks():
+    plans, _, _ = _global_plans("fixture", None, 3)
+    g = np.load(os.path.join(GOLDEN, "plans_and_blocks.npz"))
+    for r, want in enumerate(HAND_3RANK):
+        assert list(plans[r]["ranges"]) == [0, 2, 4, 5]
+        for k, v in want.items():
+            assert list(plans[r][k]) == v, (r, k)                                    # the restatement
+            assert list(g[f"fixture/s3/sym0/cm2/r{r}/plan/{k}"]) == v, (r, k)        # the reference's own code
+
+
+@pytest.mark.parametrize("kind,n", [("fixture", None), ("create_a", 1001), ("lap7", (4, 3, 6))])
+@pytest.mark.parametrize("size", [2, 3])
+def test_plan_message_free_restatement_equals_golden(kind, n, size):
+    from tests import cases
+    plans, _, _ = _global_plans(kind, n, size)
+    g = np.load(os.path.join(GOLDEN, "plans_and_blocks.npz"))
+    for r in range(size):
+        for cm in (2, 1):
+            key = f"{cases.problem_name(kind, n)}/s{size}/sym0/cm{cm}/r{r}/plan"
+            for k in cases.PLAN_KEYS:
+                assert np.array_equal(np.asarray(plans[r][k]), g[f"{key}/{k}"]), (r, cm, k)
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,n", [("lap27", (6, 5, 8)), ("powerlaw", 4000), ("lap7", (7, 6, 8))])
+@pytest.mark.parametrize("size", [2, 3, 5])
+def test_plan_message_free_restatement_equals_reference(kind, n, size):
+    """Irregular neighbourhoods (power-law: every rank talks to every other) and 5 ranks, live against the
+    reference's L2GMap.cpp under thread-ranks."""
+    from oracle import ref_api as R
+    from tests import cases
+    if not R.available():
+        pytest.skip("oracle/_ref/libspmv_ref.so not built")
+    plans, inps, _ = _global_plans(kind, n, size)
+    got = {}
+
+    def body(rank):
+        inp = inps[rank]
+        A = R.RefMatrix.create_matrix(inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                      inp["ncols_local"], [], inp["col_ghosts"], False, 2)
+        got[rank] = A.plan(0)
+        A.close()
+
+    R.run_ranks(size, body)
+    for r in range(size):
+        assert cases.same_plan(plans[r], got[r]), r
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,n", [("fixture", None), ("lap7", (4, 3, 6)), ("powerlaw", 4000)])
+@pytest.mark.parametrize("size", [1, 2, 3])
+def test_halo_data_movement_restated_equals_reference(kind, n, size):
+    """L2GMap::update (L2GMap.cpp:502-526) and L2GMap::reverse_update (collective variant, :908-923) of the
+    reference under thread-ranks against the message-free restatement, bit for bit."""
+    from oracle import plan as OP
+    from oracle import ref_api as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libspmv_ref.so not built")
+    plans, inps, _ = _global_plans(kind, n, size)
+    rng = np.random.default_rng(5)
+    vec0 = [rng.standard_normal(p["local_size"] + p["num_ghosts"]) for p in plans]
+    fwd, rev = {}, {}
+
+    def body(rank):
+        inp = inps[rank]
+        A = R.RefMatrix.create_matrix(inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                      inp["ncols_local"], [], inp["col_ghosts"], False, 2)  # collective_blocking
+        x = vec0[rank].copy()
+        A.update(x)
+        fwd[rank] = x
+        z = vec0[rank].copy()
+        A.reverse_update(z)
+        rev[rank] = z
+        A.close()
+
+    R.run_ranks(size, body)
+    want_f = [v.copy() for v in vec0]
+    OP.update(plans, want_f)
+    want_r = [v.copy() for v in vec0]
+    OP.reverse_update(plans, want_r)
+    for r in range(size):
+        assert np.array_equal(fwd[r], want_f[r]), r
+        assert np.array_equal(rev[r], want_r[r]), r
+        if size == 1:
+            assert np.array_equal(rev[r], vec0[r])  # no neighbours: a no-op
