@@ -183,6 +183,27 @@ B200_API int b200_stream_write_u32(void* stream, void* d_flag, uint32_t value);
 /* The stream does not proceed until *d_flag >= value (wrap-around compare, driver semantics). */
 B200_API int b200_stream_wait_u32_geq(void* stream, void* d_flag, uint32_t value);
 
+/* ---- kernel-driven peer halo: the same exchange as two kernels on one stream.  b200_halo_push
+ *      packs x[d_idx[k]] straight into the neighbours' staging slots (NVLink stores) and its last
+ *      CTA publishes the epoch into each neighbour's flag word; b200_halo_wait_unpack polls this
+ *      rank's flag words and copies the slot of the epoch into the ghost tail.  The epoch counter
+ *      lives in the descriptor (device memory), so a captured CUDA graph replays the pair as is.
+ *      Descriptor arrays are per neighbour, ascending rank: send_off[nnbr+1] = bounds of my packed
+ *      slices (the map's _recv_offset), land[i] = element offset of my slice in neighbour i's
+ *      slot, d_peer_slot0/1[i] and d_peer_flag[i] = its two slots and my flag word in its buffer
+ *      (mapped with b200_ipc_open), d_my_slot0/1 and d_my_flag[i] = my slots and neighbour i's
+ *      flag word in my buffer.  A pair of calls must not be mixed with the stream-memop exchange
+ *      on the same flag words. ---- */
+#define B200_HALO_MAX_NEIGHBOURS 32
+B200_API int b200_halo_desc_create(void** desc, int32_t nnbr, const int32_t* send_off, const int64_t* land,
+                          void* const* d_peer_slot0, void* const* d_peer_slot1, void* const* d_peer_flag,
+                          void* d_my_slot0, void* d_my_slot1, void* const* d_my_flag, int64_t nghosts, void* stream);
+B200_API int b200_halo_desc_destroy(void* desc);
+B200_API int b200_halo_push_f64(void* desc, int32_t n, const int32_t* d_idx, const double* d_x, void* stream);
+B200_API int b200_halo_push_f32(void* desc, int32_t n, const int32_t* d_idx, const float* d_x, void* stream);
+B200_API int b200_halo_wait_unpack_f64(void* desc, int64_t nghosts, double* d_ghost_tail, void* stream);
+B200_API int b200_halo_wait_unpack_f32(void* desc, int64_t nghosts, float* d_ghost_tail, void* stream);
+
 /* ---- CG building blocks: cg.cpp:47-85 (cblas_ddot/daxpy/dscal) and the
  *      scalar kernels of cuda/cg.cuda.cu:14-38, fused.  All scalars live in a
  *      device "state" block of B200_CG_STATE_DOUBLES doubles so the loop never
@@ -217,6 +238,21 @@ B200_API int b200_cg_update_xr_f64(int32_t n, double* d_state, const double* d_p
  * range), st[0] = rnorm_new, done = converged || iterations == kmax. */
 B200_API int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* d_p,
                          double* d_hist, int32_t hist_len, void* stream);
+
+/* The whole vector half of an iteration in ONE cooperative launch (cg.cpp:63-85): [p.Ap if need_dot, else
+ * st[1] as left by b200_csr_spmv_dot_f64], sum over the ranks, x/r update, r.r, sum over the ranks, p
+ * update, bookkeeping as b200_cg_update_p_f64.  peer_ctx: b200_peer_reduce_create context (NULL: one
+ * rank).  Grid-wide hand-overs inside the kernel; no-op once st[4] != 0.  Call after b200_cg_init_state. */
+B200_API int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x,
+                           double* d_r, double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot,
+                           void* stream);
+
+/* ---- CUDA graphs: a captured sequence of the calls above replayed with one launch (the CG loop:
+ *      all per-iteration state, halo epochs included, lives in device memory). ---- */
+B200_API int b200_graph_capture_begin(void* stream);
+B200_API int b200_graph_capture_end(void* stream, void** graph_exec);
+B200_API int b200_graph_launch(void* graph_exec, void* stream);
+B200_API int b200_graph_destroy(void* graph_exec);
 
 /* ---- synthetic operators generated on the device (bench / tests only; the
  *      host builders create_A, create_matrix, read_petsc are in include/spmv/).

@@ -84,6 +84,12 @@ public:
   /// owner-local indices to pack, neighbour by neighbour (host copy of _indexbuf)
   const std::vector<std::int32_t>& indexbuf() const { return _indexbuf_host; }
   CommunicationModel communication_model() const { return _cm; }
+  /// "kernel" (push + wait kernels over peer memory), "copy" (copy engine + stream memory operations),
+  /// "nccl" (grouped send/recv) or "none" (one rank): how update() moves the halo
+  const char* halo_mode() const
+  {
+    return _ranges.size() <= 2 ? "none" : _halo_kernel ? "kernel" : _peer_ok ? "copy" : "nccl";
+  }
 
 private:
   template <typename T>
@@ -121,6 +127,13 @@ private:
   void teardown_peer_reduce();
   template <typename T>
   void exchange_forward_peer(T* vec_data, void* stream) const;
+  template <typename T>
+  void finish_kernel_halo() const;
+  // kernel-driven exchange (b200_halo_push / b200_halo_wait_unpack): descriptor in device memory, and the
+  // ghost tail of an update whose wait + unpack is still to be enqueued (overlapping models)
+  bool _halo_kernel = false;
+  void* _halo_desc = nullptr;
+  mutable void* _pending_tail = nullptr;
   bool _peer_ok = false;
   char* _stage = nullptr;            // my staging buffer (cudaMalloc, IPC-exported)
   size_t _slot_bytes = 0;

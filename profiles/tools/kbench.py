@@ -59,6 +59,11 @@ def powerlaw(a, dev):
         if variant == 3:
             shapes += [(16384, 2, 16, 2), (16384, 2, 16, 3), (24576, 2, 16, 3), (16384, 3, 16, 3), (24576, 3, 16, 2),
                        (24576, 3, 8, 4), (12288, 2, 16, 3), (12288, 3, 16, 3), (49152, 3, 16, 1), (20480, 2, 16, 3)]
+        if variant == 8:  # split walk: A warps products, B warps sums
+            shapes = [(24576, 2, 16, 2), (24576, 3, 16, 2), (16384, 3, 16, 2), (16384, 4, 16, 2), (12288, 4, 16, 2),
+                      (20480, 3, 16, 2), (32768, 2, 16, 2), (49152, 3, 16, 1), (32768, 4, 16, 1),
+                      (16384, 3, 8, 3), (16384, 3, 8, 4), (12288, 4, 8, 4), (8192, 4, 8, 4), (24576, 2, 8, 3),
+                      (24576, 3, 8, 3)]
         if variant in (6, 7):  # warp-private pipelined walk: register-bound at 2 CTAs (16 warps) / 3 CTAs (8 warps)
             shapes = [(24576, 2, 16, 2), (24576, 3, 16, 2), (16384, 2, 16, 2), (16384, 3, 16, 2), (16384, 4, 16, 2),
                       (12288, 3, 16, 2), (12288, 4, 16, 2), (8192, 4, 16, 2), (8192, 6, 16, 2), (32768, 3, 16, 2),

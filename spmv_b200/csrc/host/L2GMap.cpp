@@ -209,6 +209,31 @@ void L2GMap::setup_peer_halo()
   int all_ok = 0;
   CHECK_MPI(MPI_Allreduce(&ok, &all_ok, 1, MPI_INT, MPI_MIN, _comm));
   _peer_ok = all_ok != 0;
+  // Kernel-driven exchange (push + wait kernels, device-side epoch; b200spmv.h): the default whenever the
+  // peers are mapped.  B200_HALO=copy keeps the copy-engine + stream-memop exchange.
+  int want_kernel = _peer_ok && nnbr >= 1 && nnbr <= B200_HALO_MAX_NEIGHBOURS && !(mode && std::strcmp(mode, "copy") == 0);
+  if (_peer_ok && nnbr == 0)
+    want_kernel = !(mode && std::strcmp(mode, "copy") == 0); // nothing to exchange: agree with the others
+  if (want_kernel && nnbr >= 1) {
+    std::vector<void*> ps0(nnbr), ps1(nnbr), pf(nnbr), mf(nnbr);
+    for (int i = 0; i < nnbr; ++i) {
+      ps0[i] = _peer_stage[i];
+      ps1[i] = _peer_stage[i] + _peer_slot_bytes[i];
+      pf[i] = _peer_stage[i] + 2 * _peer_slot_bytes[i] + sizeof(std::uint32_t) * _mpi_rank;
+      mf[i] = _stage + 2 * _slot_bytes + sizeof(std::uint32_t) * _neighbours[i];
+    }
+    if (b200_halo_desc_create(&_halo_desc, nnbr, _recv_offset.data(), _land.data(), ps0.data(), ps1.data(), pf.data(),
+                              _stage, _stage + _slot_bytes, mf.data(), static_cast<std::int64_t>(_ghosts.size()),
+                              gpu->get_cuda_stream()) != B200_OK)
+      want_kernel = 0;
+  }
+  int all_kernel = 0;
+  CHECK_MPI(MPI_Allreduce(&want_kernel, &all_kernel, 1, MPI_INT, MPI_MIN, _comm));
+  _halo_kernel = all_kernel != 0;
+  if (!_halo_kernel && _halo_desc) {
+    b200_halo_desc_destroy(_halo_desc);
+    _halo_desc = nullptr;
+  }
   if (!_peer_ok) {
     for (char*& p : _peer_stage) {
       b200_ipc_close(p);
@@ -328,6 +353,7 @@ L2GMap::~L2GMap()
   _exec->free(_indexbuf);
   _exec->free(_send_buf);
   _exec->free(_recv_buf);
+  b200_halo_desc_destroy(_halo_desc);
   for (char* p : _peer_stage)
     b200_ipc_close(p);
   if (_stage)
@@ -346,9 +372,43 @@ void L2GMap::ensure_send_buf() const
   }
 }
 //-----------------------------------------------------------------------------
+namespace
+{
+int halo_push(void* d, int n, const std::int32_t* idx, const double* x, void* st) { return b200_halo_push_f64(d, n, idx, x, st); }
+int halo_push(void* d, int n, const std::int32_t* idx, const float* x, void* st) { return b200_halo_push_f32(d, n, idx, x, st); }
+int halo_wait(void* d, std::int64_t n, double* tail, void* st) { return b200_halo_wait_unpack_f64(d, n, tail, st); }
+int halo_wait(void* d, std::int64_t n, float* tail, void* st) { return b200_halo_wait_unpack_f32(d, n, tail, st); }
+} // namespace
+//-----------------------------------------------------------------------------
+// Kernel-driven exchange: push now; the wait + unpack follows at once (blocking models) or in
+// update_finalise (overlapping models), all on the executor's stream.
+template <typename T>
+void L2GMap::finish_kernel_halo() const
+{
+  if (!_pending_tail)
+    return;
+  const B200Executor* gpu = as_b200(_exec);
+  detail::check(halo_wait(_halo_desc, static_cast<std::int64_t>(_ghosts.size()), static_cast<T*>(_pending_tail),
+                          gpu->get_cuda_stream()),
+                "halo wait + unpack");
+  _pending_tail = nullptr;
+}
+//-----------------------------------------------------------------------------
 template <typename T>
 void L2GMap::exchange_forward(T* vec_data, bool overlap) const
 {
+  if (_halo_kernel) {
+    const B200Executor* gpu = as_b200(_exec);
+    if (_neighbours.empty())
+      return;
+    detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+    finish_kernel_halo<T>(); // an exchange the caller never finalised: its slot must be drained before the next push
+    detail::check(halo_push(_halo_desc, _num_indices, _indexbuf, vec_data, gpu->get_cuda_stream()), "halo push");
+    _pending_tail = vec_data + (_ranges[_mpi_rank + 1] - _ranges[_mpi_rank]);
+    if (!overlap)
+      finish_kernel_halo<T>();
+    return;
+  }
   ensure_send_buf<T>();
   // the previous exchange may still be reading the send buffer on the side stream if the
   // caller never finalised it
@@ -403,6 +463,10 @@ void L2GMap::update_finalise(T*) const
   if (gpu == nullptr)
     throw std::runtime_error("L2GMap::update_finalise needs the B200 executor");
   detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
+  if (_halo_kernel) {
+    finish_kernel_halo<T>();
+    return;
+  }
   detail::check(b200_stream_wait_event(gpu->get_cuda_stream(), gpu->arrived_event()), "stream wait");
 }
 //-----------------------------------------------------------------------------

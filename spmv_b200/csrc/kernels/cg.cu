@@ -25,12 +25,13 @@ namespace b200
 
 // state block layout (doubles), see b200spmv.h
 enum { ST_RNORM_OLD = 0, ST_PAP = 1, ST_RR = 2, ST_RNORM0 = 3, ST_DONE = 4, ST_ITER = 5,
-       ST_RTOL = 6, ST_KMAX = 7, ST_COUNTER = 16, ST_PARTIALS = 32 };
+       ST_RTOL = 6, ST_KMAX = 7, ST_GEN = 8 /* grid-barrier generation of the fused step (u32) */,
+       ST_COUNTER = 16, ST_PARTIALS = 32 };
 
 constexpr int VEC_THREADS = 256;
 // per-CTA partials: hi parts in [0, DOT_PARTIALS), lo parts in [DOT_PARTIALS, 2*DOT_PARTIALS)
 constexpr int DOT_PARTIALS = 2000;
-static_assert(ST_PARTIALS + 2 * DOT_PARTIALS <= B200_CG_STATE_DOUBLES, "state block too small");
+static_assert(ST_PARTIALS + 2 * DOT_PARTIALS + 1 <= B200_CG_STATE_DOUBLES, "state block too small");
 static_assert(8 + 2 * DOT_PARTIALS <= B200_DOT_SCRATCH_DOUBLES, "dot scratch too small");
 
 static int vec_grid(int n)
@@ -156,20 +157,6 @@ __global__ void __launch_bounds__(VEC_THREADS)
   }
 }
 
-static int need_gpu()
-{
-  if (num_sms() <= 0) {
-    set_error("no CUDA device available: this build has no CPU path");
-    return B200_ECUDA;
-  }
-  return B200_OK;
-}
-
-} // namespace b200
-
-using namespace b200;
-
-
 // ---------------------------------------------------------------------------
 // Scalar allreduce over peer memory (the MPI_Allreduce of cg.cpp:49,65,75 on device
 // scalars).  Every rank owns a mailbox in IPC-exported device memory: one slot per
@@ -193,19 +180,19 @@ struct PeerDesc {
   PeerSlot* box[B200_PEER_REDUCE_MAX_RANKS]; // box[q] = rank q's mailbox (box[rank]: mine, local)
 };
 
-__global__ void __launch_bounds__(32) peer_allreduce_kernel(PeerDesc* d, double* val, int count)
+// One full warp.  mine[k], k < count: this rank's values; returns the sums over the ranks (all lanes).
+__device__ __forceinline__ void peer_exchange_warp(PeerDesc* d, int lane, int count,
+                                                   const double (&mine)[B200_PEER_REDUCE_MAX_COUNT],
+                                                   double (&total)[B200_PEER_REDUCE_MAX_COUNT])
 {
-  const int lane = threadIdx.x;
   const int rank = d->rank, world = d->world;
   const unsigned long long seq = d->seq + 1;
   const int par = (int)(seq & 1ull);
   __syncwarp();
-  double mine[B200_PEER_REDUCE_MAX_COUNT], got[B200_PEER_REDUCE_MAX_COUNT];
+  double got[B200_PEER_REDUCE_MAX_COUNT];
 #pragma unroll
-  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
-    mine[k] = k < count ? val[k] : 0.0;
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
     got[k] = 0.0;
-  }
   if (lane < world) {
     PeerSlot* dst = d->box[lane] + par * world + rank;
 #pragma unroll
@@ -226,15 +213,174 @@ __global__ void __launch_bounds__(32) peer_allreduce_kernel(PeerDesc* d, double*
   __syncwarp();
 #pragma unroll
   for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
-    double total = 0.0;
+    double t = 0.0;
     for (int q = 0; q < world; ++q)
-      total = add_rn(total, __shfl_sync(0xffffffffu, got[k], q));
-    if (lane == 0 && k < count)
-      val[k] = total;
+      t = add_rn(t, __shfl_sync(0xffffffffu, got[k], q));
+    total[k] = t;
   }
   if (lane == 0)
     d->seq = seq;
 }
+
+__global__ void __launch_bounds__(32) peer_allreduce_kernel(PeerDesc* d, double* val, int count)
+{
+  const int lane = threadIdx.x;
+  double mine[B200_PEER_REDUCE_MAX_COUNT], total[B200_PEER_REDUCE_MAX_COUNT];
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+    mine[k] = k < count ? val[k] : 0.0;
+  peer_exchange_warp(d, lane, count, mine, total);
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+    if (lane == 0 && k < count)
+      val[k] = total[k];
+}
+
+// ---------------------------------------------------------------------------
+// One launch for the vector half of a CG iteration (cg.cpp:63-85):
+//   [p.Ap]  ->  allreduce  ->  x += alpha p, r -= alpha Ap, r.r  ->  allreduce  ->  p = r + beta p
+// Cooperative launch (every CTA resident), grid-wide hand-over through a generation word in the
+// state block: each CTA leaves its partial, the LAST one to arrive folds them in index order,
+// exchanges the sum with the other ranks over the peer mailboxes (one warp, as above), stores the
+// global value and releases the generation; everybody else spins on it.  Replaces five launches
+// (dot, allreduce, update_xr, allreduce, update_p) whose gaps are what strong scaling at 8 GPUs
+// paid for (profiles/r01_bench_n8_strong_final.json: 0.29 ms per iteration for 0.19 ms of kernels).
+// Same arithmetic as the separate kernels: un-contracted element updates, Dot2 sums.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double fused_grid_allreduce(dd v, double* st, PeerDesc* peer, unsigned int gen_target,
+                                                       double* s_warp, double* s_bcast)
+{
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = VEC_THREADS / 32;
+  double* partials = st + ST_PARTIALS;
+  unsigned int* counter = reinterpret_cast<unsigned int*>(st + ST_COUNTER);
+  unsigned int* gen = reinterpret_cast<unsigned int*>(st + ST_GEN);
+  v = dd_warp_sum(v);
+  if (lane == 0) {
+    s_warp[2 * warp] = v.hi;
+    s_warp[2 * warp + 1] = v.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    unsigned int ticket = 0;
+    if (lane == 0) {
+      partials[blockIdx.x] = t.hi;
+      partials[DOT_PARTIALS + blockIdx.x] = t.lo;
+      __threadfence();
+      ticket = atomicAdd(counter, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) { // the last CTA: fold, exchange, publish
+      __threadfence();
+      dd s = {0.0, 0.0};
+      for (int i = lane; i < (int)gridDim.x; i += 32) {
+        dd w;
+        w.hi = __ldcg(partials + i);
+        w.lo = __ldcg(partials + DOT_PARTIALS + i);
+        s = dd_merge(s, w);
+      }
+      s = dd_warp_sum(s);
+      double mine[B200_PEER_REDUCE_MAX_COUNT] = {__dadd_rn(s.hi, s.lo), 0.0, 0.0, 0.0};
+      double total[B200_PEER_REDUCE_MAX_COUNT] = {mine[0], 0.0, 0.0, 0.0};
+      if (peer != nullptr)
+        peer_exchange_warp(peer, lane, 1, mine, total);
+      if (lane == 0) {
+        st[ST_PARTIALS + 2 * DOT_PARTIALS] = total[0];
+        *counter = 0u;
+        __threadfence();
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(gen), "r"(gen_target) : "memory");
+      }
+    }
+    if (lane == 0) {
+      unsigned int seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(gen) : "memory");
+      } while ((int)(seen - gen_target) < 0);
+      *s_bcast = __ldcg(st + ST_PARTIALS + 2 * DOT_PARTIALS);
+    }
+  }
+  __syncthreads();
+  const double out = *s_bcast;
+  __syncthreads(); // s_warp / s_bcast are free again
+  return out;
+}
+
+__global__ void __launch_bounds__(VEC_THREADS)
+    cg_fused_step_kernel(int n, double* __restrict__ st, double* __restrict__ p, const double* __restrict__ Ap,
+                         double* __restrict__ x, double* __restrict__ r, double* __restrict__ hist, int hist_len,
+                         PeerDesc* peer, int need_dot)
+{
+  __shared__ double s_warp[2 * (VEC_THREADS / 32)];
+  __shared__ double s_bcast;
+  if (st[ST_DONE] != 0.0)
+    return; // every CTA sees the same flag: it only changes at the very end of a launch
+  // read before anybody can pass the first hand-over (which needs all CTAs to have arrived)
+  const unsigned int gen0 = *reinterpret_cast<volatile unsigned int*>(st + ST_GEN);
+  const double rnorm_old = st[ST_RNORM_OLD], rnorm0 = st[ST_RNORM0], rtol = st[ST_RTOL];
+  const int stride = gridDim.x * blockDim.x;
+  const int tid0 = blockIdx.x * blockDim.x + threadIdx.x;
+
+  double pAp;
+  if (need_dot) { // cg.cpp:63-65
+    dd acc = {0.0, 0.0};
+    for (int i = tid0; i < n; i += stride)
+      dd_add_prod(acc, p[i], Ap[i]);
+    pAp = fused_grid_allreduce(acc, st, peer, gen0 + 1, s_warp, &s_bcast);
+  } else if (peer != nullptr) { // the SpMV epilogue left this rank's p.Ap in st[ST_PAP]
+    dd acc = {0.0, 0.0};
+    if (tid0 == 0)
+      acc.hi = st[ST_PAP];
+    pAp = fused_grid_allreduce(acc, st, peer, gen0 + 1, s_warp, &s_bcast);
+  } else {
+    pAp = st[ST_PAP];
+  }
+  const double alpha = (rnorm_old * rnorm_old) / pAp; // cg.cpp:66
+  const double nalpha = -alpha;
+  dd acc = {0.0, 0.0};
+  for (int i = tid0; i < n; i += stride) {
+    const double pi = p[i], api = Ap[i];
+    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, pi));              // cg.cpp:69
+    const double ri = __dadd_rn(r[i], __dmul_rn(nalpha, api)); // cg.cpp:70
+    r[i] = ri;
+    dd_add_prod(acc, ri, ri);                                  // cg.cpp:73
+  }
+  const double rr = fused_grid_allreduce(acc, st, peer, gen0 + 2, s_warp, &s_bcast);
+  const double rnorm_new = sqrt(rr);                                      // cg.cpp:76
+  const double beta = (rnorm_new * rnorm_new) / (rnorm_old * rnorm_old);  // cg.cpp:77
+  const bool converged = (rnorm_new / rnorm0) < rtol;                     // cg.cpp:80
+  if (!converged)
+    for (int i = tid0; i < n; i += stride)
+      p[i] = __dadd_rn(__dmul_rn(beta, p[i]), r[i]);                      // cg.cpp:84-85
+  if (tid0 == 0) { // nobody reads these again in this launch (everybody took its copies above)
+    const int iter = (int)st[ST_ITER] + 1;
+    st[ST_ITER] = (double)iter;
+    if (hist != nullptr && iter - 1 < hist_len)
+      hist[iter - 1] = rnorm_new;
+    st[ST_PAP] = pAp;
+    st[ST_RR] = rr;
+    st[ST_RNORM_OLD] = rnorm_new;                                         // cg.cpp:78
+    if (converged || iter >= (int)st[ST_KMAX])
+      st[ST_DONE] = 1.0;
+  }
+}
+
+static int need_gpu()
+{
+  if (num_sms() <= 0) {
+    set_error("no CUDA device available: this build has no CPU path");
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
+} // namespace b200
+
+using namespace b200;
+
 
 extern "C" {
 
@@ -290,6 +436,32 @@ int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* 
   update_p_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_r, d_p, d_hist,
                                                                       hist_len);
   B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x, double* d_r,
+                           double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot, void* stream)
+{
+  B200_REQUIRE(n >= 0 && d_state, "bad argument");
+  B200_REQUIRE(n == 0 || (d_p && d_Ap && d_x && d_r), "NULL vector");
+  if (int rc = need_gpu())
+    return rc;
+  // every CTA must be resident (they hand over through a spin): occupancy bounds the grid
+  static int per_sm[64] = {0};
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "device index out of range");
+  if (per_sm[dev] == 0) {
+    int b = 0;
+    B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, cg_fused_step_kernel, VEC_THREADS, 0));
+    B200_REQUIRE(b >= 1, "fused CG step does not fit an SM");
+    per_sm[dev] = b;
+  }
+  const int grid = std::max(1, std::min(std::min(vec_grid(n), num_sms() * per_sm[dev]), DOT_PARTIALS));
+  PeerDesc* peer = static_cast<PeerDesc*>(peer_ctx);
+  void* args[] = {&n, &d_state, &d_p, &d_Ap, &d_x, &d_r, &d_hist, &hist_len, &peer, &need_dot};
+  B200_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(cg_fused_step_kernel), dim3(grid), dim3(VEC_THREADS),
+                                        args, 0, as_stream(stream)));
   return B200_OK;
 }
 

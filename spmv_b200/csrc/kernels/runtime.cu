@@ -266,6 +266,42 @@ int b200_stream_wait_u32_geq(void* stream, void* d_flag, uint32_t value)
   return B200_OK;
 }
 
+int b200_graph_capture_begin(void* stream)
+{
+  B200_REQUIRE(stream != nullptr, "the legacy default stream cannot be captured");
+  B200_CUDA(cudaStreamBeginCapture(as_stream(stream), cudaStreamCaptureModeThreadLocal));
+  return B200_OK;
+}
+
+int b200_graph_capture_end(void* stream, void** graph_exec)
+{
+  B200_REQUIRE(graph_exec != nullptr, "graph_exec is NULL");
+  *graph_exec = nullptr;
+  cudaGraph_t g = nullptr;
+  B200_CUDA(cudaStreamEndCapture(as_stream(stream), &g));
+  cudaGraphExec_t e = nullptr;
+  const cudaError_t err = cudaGraphInstantiate(&e, g, 0);
+  cudaGraphDestroy(g);
+  if (err != cudaSuccess)
+    return cuda_fail(err, "cudaGraphInstantiate", __FILE__, __LINE__);
+  *graph_exec = e;
+  return B200_OK;
+}
+
+int b200_graph_launch(void* graph_exec, void* stream)
+{
+  B200_REQUIRE(graph_exec != nullptr, "graph_exec is NULL");
+  B200_CUDA(cudaGraphLaunch(static_cast<cudaGraphExec_t>(graph_exec), as_stream(stream)));
+  return B200_OK;
+}
+
+int b200_graph_destroy(void* graph_exec)
+{
+  if (graph_exec)
+    B200_CUDA(cudaGraphExecDestroy(static_cast<cudaGraphExec_t>(graph_exec)));
+  return B200_OK;
+}
+
 int b200_stream_destroy(void* stream)
 {
   if (stream != nullptr)

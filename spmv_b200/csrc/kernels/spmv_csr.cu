@@ -57,6 +57,9 @@ constexpr int WALK_SEG = 6;
 // the same with L1::no_allocate x gathers
 constexpr int WALK_SEGNA = 7;
 __host__ __device__ constexpr bool walk_is_seg(int w) { return w == WALK_SEG || w == WALK_SEGNA; }
+// split stream walk (general storage): half of the consumer warps make the products of tile i+1
+// while the other half sums the rows of tile i; hand-over through mbarriers only
+constexpr int WALK_SPLIT = 8;
 // WALK_SEG: ints per tile in Plan::d_warp_rows (cw + 1 row offsets, padded to a 16-byte multiple for the bulk copy)
 __host__ __device__ constexpr int seg_stride(int cw) { return (cw + 1 + 3) & ~3; }
 constexpr int SHORT_ROW = 32;  // <= this many entries: one thread walks the row
@@ -680,6 +683,136 @@ __device__ __forceinline__ dd seg_consumer(const SpmvArgs<T>& a, unsigned char* 
 }
 
 // ---------------------------------------------------------------------------
+// Split stream walk (WALK_SPLIT; general storage, irregular row lengths).  The stream walk's two
+// phases run on DIFFERENT warps, one tile apart:
+//   A warps (first half of the consumers): products.  Entry-parallel over the whole tile, every lane
+//     busy whatever the row lengths, eight independent x gathers in flight per lane; the product
+//     overwrites the staged value.  They arrive on prod[s] and go straight on to the next tile.
+//   B warps (second half): sums.  One lane per row over the WHOLE tile (a 24 KB tile of the
+//     power-law matrix has ~235 rows for 256 lanes; the warp-private walk had 15 rows per warp and
+//     ran its sum loop with 7 lanes active, profiles/r02_powerlaw_walks.md), left-to-right in chunks
+//     of eight loads then eight adds -- the reference's order (csr_kernels.cpp:45-47), rows <= 32
+//     entries bit-identical; longer rows by the warp that found them.  They arrive on empty[s].
+// Hand-over between the groups is the prod[s] mbarrier: no bar.sync anywhere, a waiting warp sleeps
+// in mbarrier.try_wait instead of holding an issue slot, and the gather latency of tile i+1 hides
+// behind the shared-memory sums of tile i by construction.
+// Padding adds of +0.0 are exact: a left-to-right sum that starts at +0.0 is never -0.0.
+// ---------------------------------------------------------------------------
+template <typename T, int NA>
+__device__ __forceinline__ void split_products(const SpmvArgs<T>& a, unsigned char* smem, StageMeta* meta, uint64_t* full,
+                                               uint64_t* prod, int my_tiles, int warp, int lane)
+{
+  constexpr int U = 8;
+  constexpr int NT = NA * 32;
+  const int stages = a.stages, sb = a.stage_bytes;
+  const int tid = warp * 32 + lane;
+  for (int it = 0, s = 0, use = 0; it < my_tiles; ++it) {
+    mbar_wait(full + s, use & 1);
+    const StageMeta* m = meta + s;
+    const int ns = m->nstaged;
+    if (ns > 0) {
+      const int r0 = m->r0, lo = m->lo, hi = m->hi;
+      const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
+      unsigned char* stage = smem + (size_t)s * sb;
+      T* sv = reinterpret_cast<T*>(stage) + (lo - L.lo_v);
+      const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c);
+      const int n = hi - lo;
+      for (int j0 = tid; j0 < n; j0 += NT * U) {
+        T xv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int j = j0 + u * NT;
+          xv[u] = j < n ? __ldg(a.x + sc[j]) : T(0);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int j = j0 + u * NT;
+          if (j < n)
+            sv[j] = mul_rn(sv[j], xv[u]);
+        }
+      }
+      fence_proxy_async_smem(); // these generic-proxy writes precede the bulk copy that will refill the stage
+    }
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(prod + s);
+    s = s + 1 == stages ? 0 : s + 1;
+    use += s == 0;
+  }
+}
+
+template <typename T, bool DOT, int NB>
+__device__ __forceinline__ dd split_sums(const SpmvArgs<T>& a, unsigned char* smem, StageMeta* meta, uint64_t* prod,
+                                         uint64_t* empty, int my_tiles, int warp, int lane, double* s_warp)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int C = 8;
+  constexpr int NT = NB * 32;
+  const int stages = a.stages, sb = a.stage_bytes;
+  const int tid = warp * 32 + lane;
+  dd dot = {0.0, 0.0};
+  for (int it = 0, s = 0, use = 0; it < my_tiles; ++it) {
+    mbar_wait(prod + s, use & 1);
+    const StageMeta* m = meta + s;
+    const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
+    if (ns > 0) {
+      const int lo = m->lo, hi = m->hi;
+      const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
+      const unsigned char* stage = smem + (size_t)s * sb;
+      const T* sv = reinterpret_cast<const T*>(stage) + (lo - L.lo_v);
+      const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r);
+      for (int k0 = warp * 32; k0 < ns; k0 += NT) {
+        const int k = k0 + lane;
+        int rs = 0, re = 0;
+        if (k < ns) {
+          rs = sr[k] - lo;
+          re = sr[k + 1] - lo;
+        }
+        const bool is_long = re - rs > SHORT_ROW;
+        if (k < ns && !is_long) {
+          T sum = T(0);
+          for (int b = rs; b < re; b += C) {
+            T pv[C];
+#pragma unroll
+            for (int u = 0; u < C; ++u)
+              pv[u] = b + u < re ? sv[b + u] : T(0);
+#pragma unroll
+            for (int u = 0; u < C; ++u)
+              sum = add_rn(sum, pv[u]);
+          }
+          const T out = store_row<T, false>(a, r0 + k, sum);
+          if (DOT)
+            dd_add_prod(dot, (double)__ldg(a.x + r0 + k), (double)out);
+        }
+        unsigned todo = __ballot_sync(FULL, is_long);
+        while (todo) {
+          const int src = __ffs(todo) - 1;
+          todo &= todo - 1;
+          const int qs = __shfl_sync(FULL, rs, src), qe = __shfl_sync(FULL, re, src);
+          T part = T(0);
+          for (int j = qs + lane; j < qe; j += 32)
+            part += sv[j];
+          part = warp_sum(part);
+          if (lane == 0) {
+            const T out = store_row<T, false>(a, r0 + k0 + src, part);
+            if (DOT)
+              dd_add_prod(dot, (double)__ldg(a.x + r0 + k0 + src), (double)out);
+          }
+        }
+      }
+    }
+    if (ns < nrows) // a row too long for a stage: straight from global memory, by the B group
+      dot = dd_merge(dot, walk_direct_cta<T, false, DOT>(a, r0 + ns, nrows - ns, tid, NT, warp, NB, lane, 1, s_warp));
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(empty + s);
+    s = s + 1 == stages ? 0 : s + 1;
+    use += s == 0;
+  }
+  return dot;
+}
+
+// ---------------------------------------------------------------------------
 // Variant 0: persistent CTAs, bulk-async staged ring, warp-specialised.
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
 //   WALK_ROW16/8/4: one thread per row (chunked gathers);  WALK_STREAM: two-phase stream walk.
@@ -688,15 +821,17 @@ __device__ __forceinline__ dd seg_consumer(const SpmvArgs<T>& a, unsigned char* 
 // tiles in flight per warp would otherwise take ~94 registers and a single CTA per SM)
 __host__ __device__ constexpr int pipe_min_ctas(bool sym, int walk, int cw)
 {
-  return (!sym && walk_is_seg(walk)) ? (cw == 16 ? 2 : 3) : 1;
+  return (!sym && (walk_is_seg(walk) || walk == WALK_SPLIT)) ? (cw == 16 ? 2 : 3) : 1;
 }
 
 template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
 __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) spmv_pipe_kernel(const SpmvArgs<T> a)
 {
   constexpr bool SEGW = !SYM && walk_is_seg(WALK); // warp-private pipelined walk (general storage only)
+  constexpr bool SPLIT = !SYM && WALK == WALK_SPLIT; // products and sums on different warps
+  constexpr int NA = CW / 2, NB = CW - NA;
   constexpr int WR_BYTES = SEGW ? seg_stride(CW) * 4 : 0;
-  constexpr int LAY = SYM ? ((WALK == WALK_STREAM || walk_is_seg(WALK)) ? LAY_DXP : LAY_DX) : LAY_PLAIN;
+  constexpr int LAY = SYM ? ((WALK == WALK_STREAM || walk_is_seg(WALK) || WALK == WALK_SPLIT) ? LAY_DXP : LAY_DX) : LAY_PLAIN;
   constexpr int CHUNK = (WALK == WALK_ROW4 || WALK == WALK_ROW4S) ? 4 : ((WALK == WALK_ROW8 || WALK == WALK_ROW8S) ? 8 : 16);
   constexpr bool SINGLE = WALK == WALK_ROW4S || WALK == WALK_ROW8S;
   extern __shared__ __align__(128) unsigned char smem[];
@@ -705,13 +840,15 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
   StageMeta* meta = reinterpret_cast<StageMeta*>(smem + (size_t)stages * sb);
   uint64_t* full = reinterpret_cast<uint64_t*>(meta + stages);
   uint64_t* empty = full + stages;
-  double* s_warp = reinterpret_cast<double*>(empty + stages);
+  uint64_t* prod = empty + stages; // SPLIT: products of the stage are in place
+  double* s_warp = reinterpret_cast<double*>(prod + stages);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(full + s, 1);
-      mbar_init(empty + s, CW);
+      mbar_init(empty + s, SPLIT ? NB : CW);
+      mbar_init(prod + s, NA);
     }
     mbar_fence_init();
   }
@@ -722,10 +859,10 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
 
   if (warp == CW) {
     if (lane == 0) {
-      const uint64_t pol_stream = (SYM || SEGW) ? l2_policy_evict_first() : 0ull;
-      const bool hint = SYM || (SEGW && (a.flags & 1));
+      const uint64_t pol_stream = (SYM || SEGW || SPLIT) ? l2_policy_evict_first() : 0ull;
+      const bool hint = SYM || ((SEGW || SPLIT) && (a.flags & 1));
       auto stream_g2s = [&](void* d, const void* g, uint32_t bytes, uint64_t* bar) {
-        if constexpr (SYM || SEGW) {
+        if constexpr (SYM || SEGW || SPLIT) {
           if (hint)
             bulk_g2s_hint(d, g, bytes, bar, pol_stream);
           else
@@ -739,14 +876,15 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
       // producer's chain per tile is not table load -> wait -> issue (~1.4 us per tile and CTA,
       // profiles/r01_powerlaw_walks.md) but max(table load, wait) -> issue
       int2 n0 = make_int2(0, 0), n1 = make_int2(0, 0);
-      if (SEGW && my_tiles > 0) {
+      constexpr bool PREFETCH = SEGW || SPLIT;
+      if (PREFETCH && my_tiles > 0) {
         n0 = __ldg(tmeta + a.tile0 + blockIdx.x);
         n1 = __ldg(tmeta + a.tile0 + blockIdx.x + 1);
       }
       for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
         const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
         int2 t0, t1;
-        if constexpr (SEGW) {
+        if constexpr (SEGW || SPLIT) {
           t0 = n0, t1 = n1;
           if (it + 1 < my_tiles) {
             n0 = __ldg(tmeta + tile + gridDim.x);
@@ -755,7 +893,7 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
         }
         if (use > 0)
           mbar_wait(empty + s, (use - 1) & 1);
-        if constexpr (!SEGW) {
+        if constexpr (!(SEGW || SPLIT)) {
           t0 = __ldg(tmeta + tile);
           t1 = __ldg(tmeta + tile + 1);
         }
@@ -807,8 +945,17 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
   // 0.85 -> 1.04 ms) with the incremental stage counters and the CTA-wide direct walk in the loop
   // body, and the 8-entry general walk ~2% better (7-point: 0.257 -> 0.251 ms), A/B-measured in
   // profiles/r01_powerlaw_walks.md; the irregular walks need the CTA-wide direct walk.
-  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || walk_is_seg(WALK) || (!SYM && CHUNK == 8);
-  if constexpr (SEGW) {
+  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || walk_is_seg(WALK) || WALK == WALK_SPLIT || (!SYM && CHUNK == 8);
+  if constexpr (SPLIT) {
+    if (warp < NA) {
+      split_products<T, NA>(a, smem, meta, full, prod, my_tiles, warp, lane);
+      if (DOT) // the reduction below counts CW warps: A warps bring zeros
+        grid_dd_reduce(dot, threadIdx.x, CW * 32, 2, s_warp, a.partials, a.partials_len, a.counter, a.dot_out);
+      return;
+    }
+    // (scratch of the direct walk behind the 2 * CW doubles the dot reduction uses: the A warps may be in it already)
+    dot = split_sums<T, DOT, NB>(a, smem, meta, prod, empty, my_tiles, warp - NA, lane, s_warp + 32);
+  } else if constexpr (SEGW) {
     dot = seg_consumer<T, DOT, CW, WALK == WALK_SEGNA>(a, smem, meta, full, empty, my_tiles, warp, lane, s_warp);
   } else
   for (int it = 0, cs = 0, cu = 0; it < my_tiles; ++it) {
@@ -824,7 +971,7 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
     StageMeta* m = meta + s;
     const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
     if (ns > 0) {
-      if (WALK == WALK_STREAM || walk_is_seg(WALK)) {
+      if (WALK == WALK_STREAM || walk_is_seg(WALK) || WALK == WALK_SPLIT) {
         dot = dd_merge(dot, walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32,
                                                            warp, CW, lane, 1));
         fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
@@ -1119,7 +1266,7 @@ static int env_int(const char* name, int dflt)
 
 static size_t pipe_smem_bytes(const Plan& p)
 {
-  return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 16 * p.stages + 8 * 32;
+  return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 24 * p.stages + 8 * 64;
 }
 
 static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
@@ -1140,7 +1287,7 @@ static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
   p->w_row = 4;
   if (p->symmetric && p->variant == 0) {
     p->w_row = 20; // rowptr + diagonal + x
-    if (p->walk == WALK_STREAM || walk_is_seg(p->walk))
+    if (p->walk == WALK_STREAM || walk_is_seg(p->walk) || p->walk == WALK_SPLIT)
       p->w_entry = 20; // value + column + product
   }
   const long long total = (long long)p->w_entry * p->nnz + (long long)p->w_row * p->rows;
@@ -1215,6 +1362,9 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
   case WALK_SEGNA:
     *tile_bytes = 16 * 1024, *stages = 3, *cw = 16, *ctas = 2;
     break;
+  case WALK_SPLIT:
+    *tile_bytes = 16 * 1024, *stages = 3, *cw = 16, *ctas = 2;
+    break;
   default:
     *tile_bytes = 48 * 1024, *cw = 8, *ctas = 2;
   }
@@ -1223,15 +1373,15 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
 // b200_csr_plan_tune's variant -> forced walk (-1: chosen from the histogram)
 static int walk_of_variant(int variant)
 {
-  return variant == 7 ? WALK_SEGNA : variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
+  return variant == 8 ? WALK_SPLIT : variant == 7 ? WALK_SEGNA : variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
 }
 
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant >= 0 && variant <= 7, "variant must be 0..7");
+  B200_REQUIRE(variant >= 0 && variant <= 8, "variant must be 0..8");
   // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
   // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4;
-  // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM); 7: WALK_SEGNA
+  // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM); 7: WALK_SEGNA; 8: WALK_SPLIT
   p->walk_forced = walk_of_variant(variant);
   if (variant >= 2)
     variant = 0;
@@ -1310,6 +1460,11 @@ static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st
       return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
     else
       return launch_pipe_cw<T, SYM, DOT, false, WALK_SEGNA>(p, a, st);
+  case WALK_SPLIT:
+    if constexpr (SYM)
+      return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
+    else
+      return launch_pipe_cw<T, SYM, DOT, false, WALK_SPLIT>(p, a, st);
   case WALK_ROW8:
     if (p.max_row_len <= 8)
       return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW8S>(p, a, st);

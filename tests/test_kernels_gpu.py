@@ -37,6 +37,10 @@ SEG_VARIANTS = [
     dict(variant=6, tile_bytes=49152, stages=4, consumer_warps=8, ctas_per_sm=1),
     dict(variant=7, tile_bytes=16384, stages=3, consumer_warps=16, ctas_per_sm=2),
     dict(variant=7, tile_bytes=1024, stages=5, consumer_warps=8, ctas_per_sm=3),
+    # 8 = split stream walk: products and sums on different warps, one tile apart
+    dict(variant=8, tile_bytes=16384, stages=3, consumer_warps=16, ctas_per_sm=2),
+    dict(variant=8, tile_bytes=24576, stages=2, consumer_warps=8, ctas_per_sm=3),
+    dict(variant=8, tile_bytes=2048, stages=4, consumer_warps=16, ctas_per_sm=2),
 ]
 
 
