@@ -66,6 +66,9 @@ public:
   void* comm_stream() const { return _comm_stream; }
   void* packed_event() const { return _ev_packed; }
   void* arrived_event() const { return _ev_arrived; }
+  /// Slot for the CG solver's cached workspace (vectors, state block, private stream, captured graph):
+  /// spmv::cg allocates it on first use and re-uses it across calls; freed with the executor.
+  std::shared_ptr<void>& cg_workspace() const { return _cg_workspace; }
   /// scatter-add used by L2GMap::reverse_update
   void scatter_add_run(int num_indices, const int32_t* indices, const float* in, float* inout) const;
   void scatter_add_run(int num_indices, const int32_t* indices, const double* in, double* inout) const;
@@ -92,6 +95,7 @@ private:
   void* _comm_stream = nullptr;
   void* _ev_packed = nullptr;
   void* _ev_arrived = nullptr;
+  mutable std::shared_ptr<void> _cg_workspace;
 };
 
 // Source compatibility with code written for the reference's CUDA backend.

@@ -29,6 +29,17 @@ SPMV_EXPORT int cg(MPI_Comm comm, B200Executor& exec, const spmv::Matrix<double>
 SPMV_EXPORT int cg(MPI_Comm comm, B200Executor& exec, const spmv::Matrix<double>& A, const double* b,
                    double* x, int kmax, double rtol, std::vector<double>* residual_history);
 
+/// Per-phase device time of one iteration, averaged over the iterations run (CUDA events, one iteration at
+/// a time): halo update (pack + push), local-block SpMV, halo wait + remote-block SpMV, vector step with its
+/// two scalar reductions.  What demos/cg.cpp's timers would show, split the way the kernels are.
+struct CgPhaseTimes {
+  int iterations = 0;
+  double us_update = 0, us_local = 0, us_remote = 0, us_vector = 0;
+};
+/// Same solve in profile mode (no graph, a host synchronisation per iteration): fills `phases`.
+SPMV_EXPORT int cg(MPI_Comm comm, B200Executor& exec, const spmv::Matrix<double>& A, const double* b,
+                   double* x, int kmax, double rtol, std::vector<double>* residual_history, CgPhaseTimes* phases);
+
 /// The host executor has no compute path: throws std::runtime_error.
 SPMV_EXPORT int cg(MPI_Comm comm, ReferenceExecutor& exec, const spmv::Matrix<double>& A, const double* b,
                    double* x, int kmax, double rtol);

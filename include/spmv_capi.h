@@ -105,6 +105,13 @@ SPMVH_API int spmvh_matrix_mult_host_f32(void* mat, const float* x_host, float* 
 SPMVH_API int spmvh_cg(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol, double* hist,
                        int hist_cap, int* iterations);
 
+/* The same solve in profile mode (one iteration at a time, CUDA events between its parts): average device
+ * microseconds per iteration of {halo update, local-block SpMV, halo wait + remote block, vector step}. */
+SPMVH_API int spmvh_cg_phases(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol,
+                              double out_us[4], int* iterations);
+/* How this map moves its halo: "kernel", "copy", "nccl" or "none" (NUL-terminated into out[cap]). */
+SPMVH_API int spmvh_l2g_halo_mode(void* map, char* out, int cap);
+
 /* ---- PETSc binary writers (inputs for read_petsc) ---- */
 SPMVH_API int spmvh_write_petsc_matrix(const char* filename, int32_t nrows, int32_t ncols, const int32_t* rowptr,
                                        const int32_t* colind, const double* values);

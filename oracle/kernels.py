@@ -122,6 +122,25 @@ def dscal(a, x):
     lib().oracle_dscal(len(x), a, x)
 
 
+def laplace3d(nx, ny, nzg, z0, z1, stencil, symmetric=False):
+    """Rows of planes [z0, z1) of the 7-/27-point Laplacian (definition: spmv_b200/synth.py::laplace3d_rows),
+    generated by the plain-C oracle_laplace3d: -> (rowptr int32, global colind int32, values[, diagonal]).
+    symmetric: strictly lower triangle + diagonal (Matrix.cpp:337-349 at one rank)."""
+    L = lib()
+    L.oracle_laplace3d.restype = C.c_longlong
+    L.oracle_laplace3d.argtypes = [C.c_int, C.c_int, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int, C.c_int,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    rows = nx * ny * (z1 - z0)
+    rp = np.zeros(rows + 1, np.int64)
+    n = L.oracle_laplace3d(nx, ny, nzg, z0, z1, stencil, int(symmetric), _ptr(rp), None, None, None)
+    assert n < 2 ** 31
+    ci, v = np.empty(n, np.int32), np.empty(n, np.float64)
+    d = np.zeros(rows, np.float64) if symmetric else None
+    L.oracle_laplace3d(nx, ny, nzg, z0, z1, stencil, int(symmetric), _ptr(rp), _ptr(ci), _ptr(v), _ptr(d))
+    rp = rp.astype(np.int32)
+    return (rp, ci, v, d) if symmetric else (rp, ci, v)
+
+
 def ref_run(rows, cols, rowptr, colind, values, diagonal, symmetric, x, alpha=1.0, beta=0.0, y=None):
     """The reference's own sequential CSRSpMV<double>::run (oracle/_ref)."""
     nnz = 0 if values is None else len(values)

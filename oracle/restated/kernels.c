@@ -133,3 +133,51 @@ void oracle_dscal(int32_t n, double a, double* x)
   for (int32_t i = 0; i < n; ++i)
     x[i] *= a;
 }
+
+/* ---- input generator for the CPU legs (bench.py cpu_baseline / --impl reference): rows of planes [z0, z1)
+ * of the 7- or 27-point Laplacian on an nx*ny*nzg grid, the same definition as spmv_b200/synth.py::
+ * laplace3d_rows (index i = x + nx*(y + ny*z), diagonal 6 / 26, neighbours -1, Dirichlet truncation),
+ * GLOBAL column ids ascending within a row.  mode 0: every entry.  mode 1: the one-rank symmetric split of
+ * Matrix.cpp:337-349 -- strictly lower triangle in (rowptr, colind, values), diagonal in diag[].
+ * Call once with colind == NULL to fill rowptr (rows + 1 entries) and get the entry count, then again with
+ * the arrays sized from it.  Plain C, one thread: 449 M entries in a couple of seconds. */
+long long oracle_laplace3d(int nx, int ny, long long nzg, long long z0, long long z1, int stencil, int mode,
+                           long long* rowptr, int* colind, double* values, double* diag)
+{
+  const double dval = stencil == 7 ? 6.0 : 26.0;
+  long long n = 0, row = 0;
+  for (long long z = z0; z < z1; ++z)
+    for (int y = 0; y < ny; ++y)
+      for (int x = 0; x < nx; ++x, ++row) {
+        const long long self = x + (long long)nx * (y + (long long)ny * z);
+        rowptr[row] = n;
+        for (int dz = -1; dz <= 1; ++dz)
+          for (int dy = -1; dy <= 1; ++dy)
+            for (int dx = -1; dx <= 1; ++dx) {
+              const int off = (dx != 0) + (dy != 0) + (dz != 0);
+              if (stencil == 7 && off > 1)
+                continue;
+              const long long zz = z + dz;
+              const int yy = y + dy, xx = x + dx;
+              if (xx < 0 || xx >= nx || yy < 0 || yy >= ny || zz < 0 || zz >= nzg)
+                continue;
+              const long long c = xx + (long long)nx * (yy + (long long)ny * zz);
+              if (mode == 1) {
+                if (c == self) {
+                  if (diag)
+                    diag[row] = dval;
+                  continue;
+                }
+                if (c > self)
+                  continue;
+              }
+              if (colind) {
+                colind[n] = (int)c;
+                values[n] = off == 0 ? dval : -1.0;
+              }
+              ++n;
+            }
+      }
+  rowptr[row] = n;
+  return n;
+}

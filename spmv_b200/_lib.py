@@ -71,6 +71,17 @@ SIGNATURES = {
     "b200_peer_reduce_destroy": [_p],
     "b200_peer_allreduce_sum_f64": [_p, _p, _i32, _p],
     "b200_cg_init_state": [_p, _p, _f64, _i32, _p],
+    "b200_cg_fused_step_f64": [_i32, _p, _p, _p, _p, _p, _p, _i32, _p, _int, _p],
+    "b200_graph_capture_begin": [_p],
+    "b200_graph_capture_end": [_p, C.POINTER(_p)],
+    "b200_graph_launch": [_p, _p],
+    "b200_graph_destroy": [_p],
+    "b200_halo_desc_create": [C.POINTER(_p), _i32, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p],
+    "b200_halo_desc_destroy": [_p],
+    "b200_halo_push_f64": [_p, _i32, _p, _p, _p],
+    "b200_halo_push_f32": [_p, _i32, _p, _p, _p],
+    "b200_halo_wait_unpack_f64": [_p, _i64, _p, _p],
+    "b200_halo_wait_unpack_f32": [_p, _i64, _p, _p],
     "b200_cg_update_xr_f64": [_i32, _p, _p, _p, _p, _p, _p],
     "b200_cg_update_p_f64": [_i32, _p, _p, _p, _p, _i32, _p],
     "b200_gen_laplace3d_rowptr": [_int, _int, _i64, _i64, _i64, _int, _int, _p, _p,

@@ -62,6 +62,8 @@ _SIG = {
     "spmvh_l2g_allreduce_f64": [_p, _p, _i32, C.c_int],
     "spmvh_matrix_tune": [_p, _int, _int, _int, _int, _int, _int],
     "spmvh_cg": [_p, _p, _p, _p, _int, _f64, _p, _int, C.POINTER(_int)],
+    "spmvh_cg_phases": [_p, _p, _p, _p, _int, _f64, C.POINTER(_f64), C.POINTER(_int)],
+    "spmvh_l2g_halo_mode": [_p, C.c_char_p, _int],
     "spmvh_l2g_update_f32": [_p, _p],
     "spmvh_l2g_update_finalise_f32": [_p, _p],
     "spmvh_l2g_reverse_update_f32": [_p, _p],
@@ -369,6 +371,11 @@ class L2GMap:
     def reverse_update(self, vec):
         _ck(getattr(host_lib(), "spmvh_l2g_reverse_update_" + self._sfx(vec))(self.h, _dev_ptr(vec)))
 
+    def halo_mode(self):
+        buf = C.create_string_buffer(16)
+        _ck(host_lib().spmvh_l2g_halo_mode(self.h, buf, 16))
+        return buf.value.decode()
+
     def allreduce_sum(self, vec, nccl=False):
         """Sum the (<= 4) doubles of `vec` over the ranks, in place, on the executor's stream."""
         _ck(host_lib().spmvh_l2g_allreduce_f64(self.h, _dev_ptr(vec), int(vec.numel()), int(bool(nccl))))
@@ -604,3 +611,11 @@ def cg(exec, A, b, x, kmax, rtol, history=False):
     if history:
         return it.value, hist[: it.value].copy()
     return it.value
+
+
+def cg_phases(exec, A, b, x, kmax, rtol=0.0):
+    """spmv::cg in profile mode -> (iterations, {"update","local","remote","vector"}: device us per iteration)."""
+    out = (_f64 * 4)()
+    it = C.c_int()
+    _ck(host_lib().spmvh_cg_phases(exec.h, A.h, _dev_ptr(b), _dev_ptr(x), int(kmax), float(rtol), out, C.byref(it)))
+    return it.value, dict(zip(("update", "local", "remote", "vector"), [float(v) for v in out]))

@@ -409,6 +409,8 @@ void L2GMap::exchange_forward(T* vec_data, bool overlap) const
       finish_kernel_halo<T>();
     return;
   }
+  if (_neighbours.empty() && _num_indices == 0)
+    return; // one rank, or a rank nobody exchanges with: nothing to pack, nothing to allocate
   ensure_send_buf<T>();
   // the previous exchange may still be reading the send buffer on the side stream if the
   // caller never finalised it

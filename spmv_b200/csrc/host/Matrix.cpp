@@ -7,6 +7,7 @@
 #include "csr_matrix.h"
 #include "device_executor.h"
 
+#include <atomic>
 #include <stdexcept>
 
 using namespace spmv;
@@ -86,12 +87,44 @@ Matrix<T> Matrix<T>::from_blocks(std::unique_ptr<SubMatrix<T>> local, std::uniqu
   return m;
 }
 //-----------------------------------------------------------------------------
+namespace spmv
+{
+namespace detail
+{
+static std::atomic<std::uint64_t> g_structure_epoch{1};
+std::uint64_t structure_epoch() { return g_structure_epoch.load(); }
+void bump_structure_epoch() { g_structure_epoch.fetch_add(1); }
+} // namespace detail
+} // namespace spmv
 template <typename T>
-Matrix<T>::~Matrix() = default;
+Matrix<T>::~Matrix()
+{
+  detail::bump_structure_epoch(); // a graph captured over this operator must not be replayed
+}
 template <typename T>
-Matrix<T>::Matrix(Matrix&&) noexcept = default;
+Matrix<T>::Matrix(Matrix&& o) noexcept
+    : _exec(std::move(o._exec)), _mat_local(std::move(o._mat_local)), _mat_remote(std::move(o._mat_remote)),
+      _col_map(std::move(o._col_map)), _row_map(std::move(o._row_map)), _nnz(o._nnz), _symmetric(o._symmetric),
+      _host_pipe(std::move(o._host_pipe))
+{
+  detail::bump_structure_epoch();
+}
 template <typename T>
-Matrix<T>& Matrix<T>::operator=(Matrix&&) noexcept = default;
+Matrix<T>& Matrix<T>::operator=(Matrix&& o) noexcept
+{
+  if (this != &o) {
+    _exec = std::move(o._exec);
+    _mat_local = std::move(o._mat_local);
+    _mat_remote = std::move(o._mat_remote);
+    _col_map = std::move(o._col_map);
+    _row_map = std::move(o._row_map);
+    _nnz = o._nnz;
+    _symmetric = o._symmetric;
+    _host_pipe = std::move(o._host_pipe);
+    detail::bump_structure_epoch();
+  }
+  return *this;
+}
 //-----------------------------------------------------------------------------
 template <typename T>
 int Matrix<T>::rows() const

@@ -312,6 +312,7 @@ int spmvh_matrix_tune(void* mat, int which, int variant, int tile_bytes, int sta
     const CSRMatrix<double>* b = block_of(as_mat(mat), which);
     if (!b || !b->op().plan())
       throw std::runtime_error("block has no B200 plan");
+    detail::bump_structure_epoch(); // the tile table a captured CG graph points at is about to be replaced
     detail::check(b200_csr_plan_tune(b->op().plan(), b->rowptr(), variant, tile_bytes, stages, consumer_warps,
                                      ctas_per_sm, nullptr),
                   "plan tune");
@@ -389,6 +390,33 @@ int spmvh_cg(void* exec, void* mat, const double* d_b, double* d_x, int kmax, do
     if (hist)
       for (int i = 0; i < std::min<int>(hist_cap, static_cast<int>(h.size())); ++i)
         hist[i] = h[i];
+  });
+}
+
+int spmvh_cg_phases(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol, double out_us[4],
+                    int* iterations)
+{
+  return guarded([&] {
+    auto* gpu = dynamic_cast<B200Executor*>(as_exec(exec).get());
+    if (!gpu)
+      throw std::runtime_error("spmv::cg needs the B200 executor (no CPU compute path)");
+    CgPhaseTimes t;
+    const int k = cg(MPI_COMM_WORLD, *gpu, as_mat(mat), d_b, d_x, kmax, rtol, nullptr, &t);
+    if (iterations)
+      *iterations = k;
+    out_us[0] = t.us_update;
+    out_us[1] = t.us_local;
+    out_us[2] = t.us_remote;
+    out_us[3] = t.us_vector;
+  });
+}
+int spmvh_l2g_halo_mode(void* map, char* out, int cap)
+{
+  return guarded([&] {
+    const char* m = as_map(map).halo_mode();
+    std::strncpy(out, m, cap > 0 ? cap - 1 : 0);
+    if (cap > 0)
+      out[cap - 1] = 0;
   });
 }
 

@@ -3,12 +3,19 @@
 // cuda/cg.cuda.cu:40-176 (what it replaces: 7 cuBLAS calls, 3 one-thread kernels and
 // 3 host synchronisations per iteration).
 //
-// Per iteration this enqueues: halo update of p, SpMV (with p.Ap folded into its
-// epilogue when the operator is a single general block), [allreduce], x/r update +
-// r.r, [allreduce], p update + scalar bookkeeping.  Nothing waits on the host: the
-// convergence test runs on the device and sets a `done` flag that turns every later
-// kernel into a no-op; the host reads the flag LOOKAHEAD iterations behind, so the
-// iteration count and x are exactly those of the reference's loop.
+// One iteration is a fixed sequence of kernels on ONE stream:
+//   halo push (pack + NVLink stores + flag)           L2GMap::update(p)        cg.cpp:59
+//   local-block SpMV [+ p.Ap in its epilogue]         Matrix::mult             cg.cpp:60
+//   halo wait + unpack, remote-block SpMV             (update_finalise, two-block operators)
+//   fused vector step: [p.Ap] -> sum over ranks -> x, r update -> r.r -> sum over ranks ->
+//     p update -> bookkeeping, one cooperative launch (b200_cg_fused_step_f64)   cg.cpp:63-85
+// Every per-iteration quantity -- scalars, convergence flag, iteration count, halo epochs,
+// allreduce sequence numbers -- lives in device memory, so GRAPH_ITERS iterations are captured
+// once into a CUDA graph and replayed; kernels are no-ops once the device-side `done` flag is
+// set, and the host reads the flag two graphs behind.  The iteration count, x and the residual
+// history are exactly those of the reference's loop.
+// The workspace (vectors, state block, private stream, events, the graph) is cached on the
+// executor: a second solve allocates nothing (the reference allocates per call, cg.cpp:39-42).
 #include <cstdlib>
 #include "cg.h"
 
@@ -20,6 +27,8 @@
 #include "reference_executor.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstring>
 #include <stdexcept>
 
 namespace spmv
@@ -27,11 +36,130 @@ namespace spmv
 
 namespace
 {
-constexpr int LOOKAHEAD = 8;
+constexpr int LOOKAHEAD = 8;   // stream path: iterations enqueued ahead of the flag the host reads
+constexpr int GRAPH_ITERS = 8; // iterations per captured graph
 
 struct Flags {
   double done;
   double iter;
+};
+
+bool env_flag(const char* name, bool dflt)
+{
+  const char* e = std::getenv(name);
+  return (e && *e) ? *e != '0' : dflt;
+}
+
+struct CgWorkspace {
+  int device = -1;
+  int M = -1, N_padded = -1, hist_cap = 0;
+  double *r = nullptr, *Ap = nullptr, *x_padded = nullptr, *p = nullptr, *state = nullptr, *scratch = nullptr,
+         *hist = nullptr;
+  Flags* h_flags = nullptr; // pinned, LOOKAHEAD slots
+  void* events[LOOKAHEAD] = {};
+  void* stream = nullptr;   // private stream: the legacy default stream cannot be captured
+  void* ev_in = nullptr;
+  void* graph = nullptr;    // GRAPH_ITERS iterations, instantiated
+  const void* graph_matrix = nullptr;
+  std::uint64_t graph_epoch = 0; // detail::structure_epoch() at capture
+  int graph_mode = -1;
+
+  void drop_graph()
+  {
+    if (graph)
+      b200_graph_destroy(graph);
+    graph = nullptr;
+    graph_matrix = nullptr;
+    graph_mode = -1;
+  }
+  void release()
+  {
+    if (graph_mode == -2)
+      graph_mode = -1;
+    if (device >= 0)
+      b200_set_device(device);
+    drop_graph();
+    for (double** q : {&r, &Ap, &x_padded, &p, &state, &scratch, &hist}) {
+      b200_free(*q);
+      *q = nullptr;
+    }
+    b200_host_free_pinned(h_flags);
+    h_flags = nullptr;
+    for (void*& e : events) {
+      b200_event_destroy(e);
+      e = nullptr;
+    }
+    b200_event_destroy(ev_in);
+    ev_in = nullptr;
+    if (stream)
+      b200_stream_destroy(stream);
+    stream = nullptr;
+    M = N_padded = -1;
+    hist_cap = 0;
+  }
+  ~CgWorkspace() { release(); }
+};
+
+double* dalloc(size_t n)
+{
+  void* q = nullptr;
+  detail::check(b200_malloc(&q, sizeof(double) * std::max<size_t>(n, 1)), "cg workspace");
+  return static_cast<double*>(q);
+}
+
+CgWorkspace& workspace(B200Executor& exec, int M, int N_padded, int hist_len)
+{
+  std::shared_ptr<void>& slot = exec.cg_workspace();
+  if (!slot)
+    slot = std::make_shared<CgWorkspace>();
+  CgWorkspace& w = *static_cast<CgWorkspace*>(slot.get());
+  if (w.device != exec.get_device_id() || w.M != M || w.N_padded != N_padded) {
+    w.release();
+    w.device = exec.get_device_id();
+    w.M = M;
+    w.N_padded = N_padded;
+    w.r = dalloc(M);
+    w.Ap = dalloc(M);
+    w.x_padded = dalloc(N_padded);
+    w.p = dalloc(N_padded);
+    w.state = dalloc(B200_CG_STATE_DOUBLES);
+    w.scratch = dalloc(B200_DOT_SCRATCH_DOUBLES);
+    detail::check(b200_host_alloc_pinned(reinterpret_cast<void**>(&w.h_flags), sizeof(Flags) * LOOKAHEAD), "pinned alloc");
+    for (void*& e : w.events)
+      detail::check(b200_event_create(&e, 0), "event");
+    detail::check(b200_event_create(&w.ev_in, 0), "event");
+    detail::check(b200_stream_create(&w.stream), "stream");
+    // the grid-barrier generation and the ticket counters start at zero, once
+    detail::check(b200_memset_async(w.state, 0, sizeof(double) * B200_CG_STATE_DOUBLES, w.stream), "memset");
+    detail::check(b200_memset_async(w.scratch, 0, sizeof(double) * B200_DOT_SCRATCH_DOUBLES, w.stream), "memset");
+  }
+  if (hist_len > w.hist_cap) { // the graph carries the history pointer: a new buffer needs a new capture
+    w.drop_graph();
+    b200_free(w.hist);
+    w.hist_cap = std::max(hist_len, 1024);
+    w.hist = dalloc(w.hist_cap);
+  }
+  return w;
+}
+
+// The solve runs on the workspace's private stream: point the executor(s) at it for the duration.
+struct StreamScope {
+  B200Executor *a, *b;
+  B200Executor::stream_t sa, sb;
+  StreamScope(B200Executor* a_, B200Executor* b_, void* s) : a(a_), b(b_ == a_ ? nullptr : b_), sa(a_->get_cuda_stream()), sb(nullptr)
+  {
+    a->set_cuda_stream(static_cast<B200Executor::stream_t>(s));
+    if (b) {
+      sb = b->get_cuda_stream();
+      b->set_cuda_stream(static_cast<B200Executor::stream_t>(s));
+    }
+  }
+  ~StreamScope()
+  {
+    a->set_cuda_stream(sa);
+    if (b)
+      b->set_cuda_stream(sb);
+  }
 };
 } // namespace
 
@@ -49,16 +177,36 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
 int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double* b, double* x, int kmax,
        double rtol, std::vector<double>* residual_history)
 {
+  return cg(comm, exec, A, b, x, kmax, rtol, residual_history, nullptr);
+}
+
+int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double* b, double* x, int kmax,
+       double rtol, std::vector<double>* residual_history, CgPhaseTimes* phases)
+{
   std::shared_ptr<const L2GMap> col_l2g = A.col_map();
   std::shared_ptr<const L2GMap> row_l2g = A.row_map();
   if (row_l2g->num_ghosts() > 0)
     throw std::runtime_error("spmv::cg - Error: A.row_map() has ghost entries");
   exec.attach_comm(comm);
   detail::check(b200_set_device(exec.get_device_id()), "cudaSetDevice");
-  void* stream = exec.get_cuda_stream();
   void* nccl = exec.nccl_comm();
-  // scalar sums: one small kernel over peer memory when the column map set it up, else NCCL
+  // scalar sums: over peer memory when the column map set it up, else NCCL
   void* peer = col_l2g->peer_reduce();
+
+  const int M = row_l2g->local_size();
+  const int N_padded = col_l2g->local_size() + col_l2g->num_ghosts();
+  CgWorkspace& w = workspace(exec, M, N_padded, std::max(kmax, 0));
+  double *r = w.r, *Ap = w.Ap, *x_padded = w.x_padded, *p = w.p, *state = w.state, *scratch = w.scratch, *hist = w.hist;
+  const int hist_len = w.hist_cap;
+
+  // the private stream starts after whatever the caller has queued on the executor's stream
+  void* user_stream = exec.get_cuda_stream();
+  void* stream = w.stream;
+  detail::check(b200_event_record(w.ev_in, user_stream), "event record");
+  detail::check(b200_stream_wait_event(stream, w.ev_in), "stream wait");
+  auto* mat_exec = dynamic_cast<B200Executor*>(A.executor().get());
+  StreamScope scope(&exec, mat_exec ? mat_exec : &exec, stream);
+
   auto allreduce = [&](double* d_val) {
     if (peer)
       detail::check(b200_peer_allreduce_sum_f64(peer, d_val, 1, stream), "cg allreduce (peer)");
@@ -66,115 +214,196 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
       detail::check(b200_allreduce_sum_f64(nccl, d_val, 1, stream), "cg allreduce");
   };
 
-  const int M = row_l2g->local_size();
-  const int N_padded = col_l2g->local_size() + col_l2g->num_ghosts();
-  const int hist_len = residual_history ? std::max(kmax, 0) : 0;
+  // x0 = 0, explicitly (the reference relies on the allocator for this, cg.cpp:41)
+  detail::check(b200_memset_async(x_padded, 0, sizeof(double) * N_padded, stream), "memset");
+  detail::check(b200_memset_async(p, 0, sizeof(double) * N_padded, stream), "memset");
+  detail::check(b200_memset_async(hist, 0, sizeof(double) * hist_len, stream), "memset");
+  detail::check(b200_memcpy_d2d_async(r, b, sizeof(double) * M, stream), "copy"); // cg.cpp:44-45
+  detail::check(b200_memcpy_d2d_async(p, b, sizeof(double) * M, stream), "copy");
 
-  double* r = exec.alloc<double>(std::max(M, 1));
-  double* Ap = exec.alloc<double>(std::max(M, 1));
-  double* x_padded = exec.alloc<double>(std::max(N_padded, 1));
-  double* p = exec.alloc<double>(std::max(N_padded, 1));
-  double* state = exec.alloc<double>(B200_CG_STATE_DOUBLES);
-  double* scratch = exec.alloc<double>(B200_DOT_SCRATCH_DOUBLES);
-  double* hist = hist_len > 0 ? exec.alloc<double>(hist_len) : nullptr;
-  Flags* h_flags = nullptr;
-  detail::check(b200_host_alloc_pinned(reinterpret_cast<void**>(&h_flags), sizeof(Flags) * LOOKAHEAD),
-                "pinned alloc");
-  void* events[LOOKAHEAD];
-  for (void*& e : events)
-    detail::check(b200_event_create(&e, 0), "event");
+  // rnorm0 = sqrt(allreduce(r.r))  (cg.cpp:47-50)
+  detail::check(b200_cg_dot_f64(M, r, r, state + 2, scratch, nullptr, stream), "cg dot");
+  allreduce(state + 2);
+  detail::check(b200_cg_init_state(state, state + 2, rtol, kmax, stream), "cg init");
 
-  auto cleanup = [&]() {
-    exec.free(r);
-    exec.free(Ap);
-    exec.free(x_padded);
-    exec.free(p);
-    exec.free(state);
-    exec.free(scratch);
-    exec.free(hist);
-    b200_host_free_pinned(h_flags);
-    for (void* e : events)
-      b200_event_destroy(e);
-  };
-
-  int iterations = 0;
-  try {
-    // x0 = 0, explicitly (the reference relies on the allocator for this, cg.cpp:41)
-    exec.memset<double>(x_padded, 0, N_padded);
-    exec.memset<double>(p, 0, N_padded);
-    exec.memset<double>(state, 0, B200_CG_STATE_DOUBLES);
-    exec.memset<double>(scratch, 0, B200_DOT_SCRATCH_DOUBLES);
-    if (hist)
-      exec.memset<double>(hist, 0, hist_len);
-    exec.copy<double>(r, b, M); // cg.cpp:44-45
-    exec.copy<double>(p, b, M);
-
-    // rnorm0 = sqrt(allreduce(r.r))  (cg.cpp:47-50)
-    detail::check(b200_cg_dot_f64(M, r, r, state + 2, scratch, nullptr, stream), "cg dot");
-    allreduce(state + 2);
-    detail::check(b200_cg_init_state(state, state + 2, rtol, kmax, stream), "cg init");
-
-    // fused p.Ap epilogue: single general block only
-    const CSRMatrix<double>* single = nullptr;
-    if (!A.symmetric() && A.remote_block() == nullptr)
-      single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
-    if (single && (single->non_zeros() == 0 || single->op().plan() == nullptr))
+  // fused p.Ap epilogue: single general block only.  It pays only where the SpMV instantiation keeps its
+  // occupancy with the extra registers: stencil-length rows (16-entry walk; 27-point 256^3: 1.157 vs
+  // 1.150 ms/iteration, one launch fewer).  With short rows the dot-carrying 8-entry walk loses a resident
+  // CTA per SM (7-point general 256^3: 0.74 -> 0.56 ms/iteration, profiles/r01_cg_fused_dot_ab.txt).
+  // B200_CG_FUSED_DOT=0/1 forces either.
+  const CSRMatrix<double>* single = nullptr;
+  if (!A.symmetric() && A.remote_block() == nullptr)
+    single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
+  if (single && (single->non_zeros() == 0 || single->op().plan() == nullptr))
+    single = nullptr;
+  if (single) {
+    const double mean_row = (double)single->non_zeros() / (double)std::max(M, 1);
+    if (!env_flag("B200_CG_FUSED_DOT", mean_row > 10.0))
       single = nullptr;
-    // The epilogue pays only where the SpMV instantiation keeps its occupancy with the extra
-    // registers: stencil-length rows (16-entry walk; 27-point 256^3: 1.157 vs 1.150 ms/iteration,
-    // one launch fewer).  With short rows the dot-carrying 8-entry walk loses a resident CTA per
-    // SM and a separate 31 us dot kernel wins (7-point general 256^3: 0.74 -> 0.56 ms/iteration,
-    // profiles/r01_cg_fused_dot_ab.txt).  B200_CG_FUSED_DOT=0/1 forces either.
-    if (single) {
-      const double mean_row = (double)single->non_zeros() / (double)std::max(M, 1);
-      bool fused = mean_row > 10.0;
-      if (const char* e = std::getenv("B200_CG_FUSED_DOT"))
-        fused = *e != '0';
-      if (!fused)
-        single = nullptr;
-    }
+  }
+  // vector half of the iteration in one cooperative launch: needs the peer mailboxes (or one rank); the
+  // NCCL fallback keeps the separate kernels.  Default: on when there is more than one rank (where the
+  // launch gaps between five small kernels cost more than they do at one rank); B200_CG_FUSED_VEC forces.
+  const bool can_fuse = peer != nullptr || exec.comm_size() == 1;
+  const bool fused_vec = can_fuse && env_flag("B200_CG_FUSED_VEC", exec.comm_size() > 1);
+  // CUDA graph of GRAPH_ITERS iterations: everything the iteration enqueues must be a kernel with
+  // device-side state, i.e. the kernel-driven halo (or no halo) and no NCCL call
+  const char* hm = col_l2g->halo_mode();
+  const bool graphable = (std::strcmp(hm, "kernel") == 0 || std::strcmp(hm, "none") == 0) && (peer != nullptr || exec.comm_size() == 1);
+  const bool use_graph = graphable && phases == nullptr && env_flag("B200_CG_GRAPH", true);
 
-    bool stop = false;
-    for (int k = 0; k < kmax && !stop; ++k) {
-      const int slot = k % LOOKAHEAD;
-      if (k >= LOOKAHEAD) {
-        detail::check(b200_event_synchronize(events[slot]), "event sync");
-        if (h_flags[slot].done != 0.0)
-          break;
-      }
-      col_l2g->update(p); // cg.cpp:59
-      if (single) {       // cg.cpp:60-63
-        detail::check(b200_csr_spmv_dot_f64(single->op().plan(), single->rowptr(), single->colind(),
-                                            single->values(), p, Ap, state + 1, stream),
-                      "cg spmv+dot");
-      } else {
-        A.mult(p, Ap);
+  // ---- one iteration, enqueued on `stream` (cg.cpp:59-85) ----
+  void* ev[6] = {};
+  auto mark = [&](int i) {
+    if (phases)
+      detail::check(b200_event_record(ev[i], stream), "event record");
+  };
+  auto iteration = [&]() {
+    mark(0);
+    col_l2g->update(p); // cg.cpp:59
+    mark(1);
+    if (single) { // cg.cpp:60-63
+      detail::check(b200_csr_spmv_dot_f64(single->op().plan(), single->rowptr(), single->colind(), single->values(), p,
+                                          Ap, state + 1, stream),
+                    "cg spmv+dot");
+      mark(2);
+      mark(3);
+    } else if (phases && A.remote_block() != nullptr) { // Matrix::mult, opened up to time its parts
+      A.local_block()->mult(1, p, 0, Ap);
+      mark(2);
+      col_l2g->update_finalise(p);
+      if (A.symmetric() || col_l2g->overlapping())
+        A.remote_block()->mult(1, p, (A.symmetric() || A.local_block()->non_zeros() > 0) ? 1.0 : 0.0, Ap);
+      mark(3);
+    } else {
+      A.mult(p, Ap);
+      mark(2);
+      mark(3);
+    }
+    if (fused_vec) {
+      detail::check(b200_cg_fused_step_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, single ? 0 : 1, stream),
+                    "cg fused step");
+    } else {
+      if (!single)
         detail::check(b200_cg_dot_f64(M, p, Ap, state + 1, scratch, state + 4, stream), "cg dot");
-      }
       allreduce(state + 1); // cg.cpp:65
       detail::check(b200_cg_update_xr_f64(M, state, p, Ap, x_padded, r, stream), "cg update x,r");
       allreduce(state + 2); // cg.cpp:75
       detail::check(b200_cg_update_p_f64(M, state, r, p, hist, hist_len, stream), "cg update p");
-      detail::check(b200_memcpy_d2h_async(&h_flags[slot], state + 4, sizeof(Flags), stream), "flag copy");
-      detail::check(b200_event_record(events[slot], stream), "event record");
     }
-    Flags last;
-    detail::check(b200_memcpy_d2h_async(&last, state + 4, sizeof(Flags), stream), "flag copy");
-    detail::check(b200_stream_synchronize(stream), "cg sync");
-    iterations = static_cast<int>(last.iter);
+    mark(4);
+  };
 
-    exec.copy<double>(x, x_padded, M); // cg.cpp:89
-    if (residual_history) {
-      residual_history->assign(iterations, 0.0);
-      if (iterations > 0)
-        exec.copy_to<double>(residual_history->data(), exec.get_host(), hist, iterations);
+  int iterations = 0;
+  Flags last;
+  if (phases) {
+    // ---- profile mode: one iteration at a time, CUDA events between its parts ----
+    for (void*& e : ev)
+      detail::check(b200_event_create(&e, 1), "event");
+    double acc[4] = {0, 0, 0, 0};
+    int done_its = 0;
+    for (int k = 0; k < kmax; ++k) {
+      iteration();
+      detail::check(b200_memcpy_d2h_async(&last, state + 4, sizeof(Flags), stream), "flag copy");
+      detail::check(b200_stream_synchronize(stream), "cg sync");
+      for (int i = 0; i < 4; ++i) {
+        float ms = 0.f;
+        detail::check(b200_event_elapsed_ms(ev[i], ev[i + 1], &ms), "event elapsed");
+        acc[i] += ms;
+      }
+      ++done_its;
+      if (last.done != 0.0)
+        break;
     }
-    detail::check(b200_stream_synchronize(stream), "cg sync");
-  } catch (...) {
-    cleanup();
-    throw;
+    for (void* e : ev)
+      b200_event_destroy(e);
+    const double s = done_its > 0 ? 1e3 / done_its : 0.0;
+    phases->iterations = done_its;
+    phases->us_update = acc[0] * s;
+    phases->us_local = acc[1] * s;
+    phases->us_remote = acc[2] * s;
+    phases->us_vector = acc[3] * s;
   }
-  cleanup();
+  // The first iteration always goes out un-captured: it runs whatever the path initialises lazily (kernel
+  // attributes, occupancy queries, buffers), none of which may happen inside a capture.
+  if (!phases && kmax > 0)
+    iteration();
+  bool graph_ready = false;
+  if (!phases && use_graph && kmax > 1 && w.graph_mode != -2) {
+    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0);
+    graph_ready = w.graph != nullptr && w.graph_matrix == static_cast<const void*>(&A) && w.graph_mode == mode
+                  && w.graph_epoch == detail::structure_epoch();
+    if (!graph_ready) {
+      w.drop_graph();
+      detail::check(b200_stream_synchronize(stream), "cg sync");
+      try { // capture enqueues nothing: if anything on the path cannot be captured, the stream path below runs instead
+        detail::check(b200_graph_capture_begin(stream), "graph capture");
+        try {
+          for (int i = 0; i < GRAPH_ITERS; ++i)
+            iteration();
+        } catch (...) {
+          void* dead = nullptr;
+          b200_graph_capture_end(stream, &dead);
+          b200_graph_destroy(dead);
+          throw;
+        }
+        detail::check(b200_graph_capture_end(stream, &w.graph), "graph instantiate");
+        w.graph_matrix = &A;
+        w.graph_mode = mode;
+        w.graph_epoch = detail::structure_epoch();
+        graph_ready = true;
+      } catch (const std::exception& e) {
+        if (env_flag("B200_CG_GRAPH_STRICT", false))
+          throw;
+        if (env_flag("B200_CG_DEBUG", false))
+          std::fprintf(stderr, "spmv::cg: graph capture failed (%s); using the stream path\n", e.what());
+        w.drop_graph();
+        w.graph_mode = -2; // do not try again with this workspace
+      }
+    }
+  }
+  if (phases) {
+  } else if (graph_ready) {
+    // ---- GRAPH_ITERS iterations per launch; the flag of graph g is read before graph g+2 goes out ----
+    for (int g = 0;; ++g) {
+      const int slot = g % LOOKAHEAD;
+      if (g >= 2) {
+        const int seen = (g - 2) % LOOKAHEAD;
+        detail::check(b200_event_synchronize(w.events[seen]), "event sync");
+        if (w.h_flags[seen].done != 0.0)
+          break;
+      }
+      if (1 + g * GRAPH_ITERS >= kmax)
+        break;
+      detail::check(b200_graph_launch(w.graph, stream), "graph launch");
+      detail::check(b200_memcpy_d2h_async(&w.h_flags[slot], state + 4, sizeof(Flags), stream), "flag copy");
+      detail::check(b200_event_record(w.events[slot], stream), "event record");
+    }
+  } else {
+    // ---- stream path: iterations enqueued LOOKAHEAD ahead of the flag the host reads ----
+    for (int k = 1; k < kmax; ++k) {
+      const int slot = k % LOOKAHEAD;
+      if (k > LOOKAHEAD) {
+        detail::check(b200_event_synchronize(w.events[slot]), "event sync");
+        if (w.h_flags[slot].done != 0.0)
+          break;
+      }
+      iteration();
+      detail::check(b200_memcpy_d2h_async(&w.h_flags[slot], state + 4, sizeof(Flags), stream), "flag copy");
+      detail::check(b200_event_record(w.events[slot], stream), "event record");
+    }
+  }
+  detail::check(b200_memcpy_d2h_async(&last, state + 4, sizeof(Flags), stream), "flag copy");
+  detail::check(b200_stream_synchronize(stream), "cg sync");
+  iterations = static_cast<int>(last.iter);
+
+  detail::check(b200_memcpy_d2d_async(x, x_padded, sizeof(double) * M, stream), "copy"); // cg.cpp:89
+  if (residual_history) {
+    residual_history->assign(iterations, 0.0);
+    if (iterations > 0)
+      detail::check(b200_memcpy_d2h_async(residual_history->data(), hist, sizeof(double) * iterations, stream), "copy");
+  }
+  detail::check(b200_stream_synchronize(stream), "cg sync");
   return iterations;
 }
 

@@ -104,6 +104,7 @@ B200Executor::B200Executor(int device_id, std::shared_ptr<DeviceExecutor> host) 
 B200Executor::~B200Executor()
 {
   b200_set_device(_dev_info.id);
+  _cg_workspace.reset(); // device memory, stream, graph: before the communicator and the streams go
   if (_nccl)
     b200_nccl_comm_destroy(_nccl);
   b200_event_destroy(_ev_packed);

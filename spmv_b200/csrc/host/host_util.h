@@ -33,6 +33,11 @@ inline std::vector<std::int64_t> owner_ranges(int size, std::int64_t N)
   return ranges;
 }
 
+/// Bumped whenever device arrays or launch plans a captured CUDA graph may have baked in go away or change
+/// (a Matrix is destroyed or moved, a plan is re-tuned): cached graphs compare it with the value at capture.
+std::uint64_t structure_epoch();
+void bump_structure_epoch();
+
 /// Threads for the host-side builders: SPMV_HOST_THREADS if set, else the CPUs this process may run
 /// on divided by `sharers` (ranks doing the same work at the same time).  Launchers such as torchrun
 /// export OMP_NUM_THREADS=1, which would serialise a 50 M-row setup; the builders pass this count to

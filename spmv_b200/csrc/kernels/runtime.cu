@@ -278,7 +278,15 @@ int b200_graph_capture_end(void* stream, void** graph_exec)
   B200_REQUIRE(graph_exec != nullptr, "graph_exec is NULL");
   *graph_exec = nullptr;
   cudaGraph_t g = nullptr;
-  B200_CUDA(cudaStreamEndCapture(as_stream(stream), &g));
+  {
+    const cudaError_t err = cudaStreamEndCapture(as_stream(stream), &g);
+    if (err != cudaSuccess) {
+      cudaGetLastError(); // an invalidated capture must not leave its error for the next launch check to find
+      if (g)
+        cudaGraphDestroy(g);
+      return cuda_fail(err, "cudaStreamEndCapture", __FILE__, __LINE__);
+    }
+  }
   cudaGraphExec_t e = nullptr;
   const cudaError_t err = cudaGraphInstantiate(&e, g, 0);
   cudaGraphDestroy(g);

@@ -817,6 +817,141 @@ __device__ __forceinline__ dd split_sums(const SpmvArgs<T>& a, unsigned char* sm
 //   warps [0, CW): consumers;  warp CW: producer (lane 0 only).
 //   WALK_ROW16/8/4: one thread per row (chunked gathers);  WALK_STREAM: two-phase stream walk.
 // ---------------------------------------------------------------------------
+// ---------------------------------------------------------------------------
+// Two kernels share the pipeline design.  spmv_pipe_kernel carries the row walks and the CTA-wide
+// stream walk and is kept EXACTLY as tuned in round 1: ptxas' register allocation for it is fragile
+// (adding the split walk's third barrier array and tile-order variables to the same function took the
+// 27-point kernel from 96 to 120 registers and the symmetric 7-point one from 56 to 64 -- one resident
+// CTA per SM instead of two, 0.85 -> 1.42 ms and 0.215 -> 0.365 ms).  spmv_irr_kernel below is the same
+// pipeline generalised for the irregular-row walks of general storage (WALK_SEG, WALK_SEGNA, WALK_SPLIT).
+// ---------------------------------------------------------------------------
+template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
+__global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs<T> a)
+{
+  constexpr int LAY = SYM ? (WALK == WALK_STREAM ? LAY_DXP : LAY_DX) : LAY_PLAIN;
+  constexpr int CHUNK = (WALK == WALK_ROW4 || WALK == WALK_ROW4S) ? 4 : ((WALK == WALK_ROW8 || WALK == WALK_ROW8S) ? 8 : 16);
+  constexpr bool SINGLE = WALK == WALK_ROW4S || WALK == WALK_ROW8S;
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int stages = a.stages;
+  const int sb = a.stage_bytes;
+  StageMeta* meta = reinterpret_cast<StageMeta*>(smem + (size_t)stages * sb);
+  uint64_t* full = reinterpret_cast<uint64_t*>(meta + stages);
+  uint64_t* empty = full + stages;
+  double* s_warp = reinterpret_cast<double*>(empty + stages);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, CW);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int span = a.num_tiles - a.tile0;
+  const int my_tiles = ((int)blockIdx.x < span) ? (span - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp == CW) {
+    if (lane == 0) {
+      const uint64_t pol_stream = SYM ? l2_policy_evict_first() : 0ull;
+      auto stream_g2s = [&](void* d, const void* g, uint32_t bytes, uint64_t* bar) {
+        if constexpr (SYM)
+          bulk_g2s_hint(d, g, bytes, bar, pol_stream);
+        else
+          bulk_g2s(d, g, bytes, bar);
+      };
+      for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
+        if (use > 0)
+          mbar_wait(empty + s, (use - 1) & 1);
+        const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
+        const int2 t0 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile);
+        const int2 t1 = __ldg(reinterpret_cast<const int2*>(a.tile_meta) + tile + 1);
+        const int r0 = t0.x, lo = t0.y, nrows = t1.x - t0.x;
+        // Stage the longest prefix of rows that fits: a tile overshoots its byte
+        // budget by at most its last row, so this drops one (long) row at most.
+        int ns = nrows, hi = t1.y;
+        while (ns > 0 && !tile_fits<T, LAY>(r0, ns, lo, hi, sb)) {
+          --ns;
+          hi = __ldg(a.rowptr + r0 + ns);
+        }
+        StageMeta* m = meta + s;
+        m->r0 = r0;
+        m->nrows = nrows;
+        m->lo = lo;
+        m->hi = hi;
+        m->nstaged = ns;
+        m->nlong = 0;
+        if (ns > 0) {
+          const TileLayout<T, LAY> L(r0, ns, lo, hi);
+          unsigned char* dst = smem + (size_t)s * sb;
+          mbar_arrive_expect_tx(full + s, (uint32_t)L.loaded());
+          // Symmetric storage: the matrix is read once per SpMV, while the y lines are touched several
+          // times (zero-fill, the row's own add, the adds from the rows that list it).  evict_first on
+          // the matrix stream keeps it from displacing them in L2: sym 7-pt 0.220 -> 0.213 ms, sym 27-pt
+          // 0.64 -> 0.62 (profiles/r01_exp_evict_first_probe.txt).  General storage gains nothing
+          // (7-pt 0.2526 vs 0.2515, 27-pt 0.864 vs 0.849) and keeps the default policy.
+          if (L.bytes_v > 0)
+            stream_g2s(dst, a.val + L.lo_v, L.bytes_v, full + s);
+          if (L.bytes_c > 0)
+            stream_g2s(dst + L.off_c(), a.colind + L.lo_c, L.bytes_c, full + s);
+          stream_g2s(dst + L.off_r(), a.rowptr + L.lo_r, L.bytes_r, full + s);
+          if (LAY >= LAY_DX) {
+            stream_g2s(dst + L.off_d(), a.diag + L.lo_d, L.bytes_d, full + s);
+            bulk_g2s(dst + L.off_x(), a.x + L.lo_d, L.bytes_d, full + s);
+          }
+        } else {
+          mbar_arrive(full + s);
+        }
+      }
+    }
+    return;
+  }
+
+  dd dot = {0.0, 0.0};
+  // Two spellings of the same loop.  ptxas schedules the 16-entry row walk ~20% worse (27-point:
+  // 0.85 -> 1.04 ms) with the incremental stage counters and the CTA-wide direct walk in the loop
+  // body, and the 8-entry general walk ~2% better (7-point: 0.257 -> 0.251 ms), A/B-measured in
+  // profiles/r01_powerlaw_walks.md; the irregular walks need the CTA-wide direct walk.
+  constexpr bool CTA_DIRECT = WALK == WALK_STREAM || (!SYM && CHUNK == 8);
+  for (int it = 0, cs = 0, cu = 0; it < my_tiles; ++it) {
+    int s, use;
+    if constexpr (CTA_DIRECT) {
+      s = cs, use = cu;
+      cs = cs + 1 == stages ? 0 : cs + 1;
+      cu += cs == 0;
+    } else {
+      s = it % stages, use = it / stages;
+    }
+    mbar_wait(full + s, use & 1);
+    StageMeta* m = meta + s;
+    const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
+    if (ns > 0) {
+      if (WALK == WALK_STREAM) {
+        dot = dd_merge(dot, walk_stream<T, SYM, LONG, DOT>(a, smem + (size_t)s * sb, m, threadIdx.x, CW * 32,
+                                                           warp, CW, lane, 1));
+        fence_proxy_async_smem(); // our generic-proxy writes precede the next bulk copy into this stage
+      } else {
+        dot = dd_merge(dot, walk_staged<T, SYM, LONG, DOT, CHUNK, LAY, SINGLE>(a, smem + (size_t)s * sb, m,
+                                                                               threadIdx.x, CW * 32, warp, CW, lane, 1));
+      }
+    }
+    if (ns < nrows) {
+      if constexpr (CTA_DIRECT)
+        dot = dd_merge(dot, walk_direct_cta<T, SYM, DOT>(a, r0 + ns, nrows - ns, threadIdx.x, CW * 32, warp, CW,
+                                                         lane, 1, s_warp));
+      else
+        dot = dd_merge(dot, walk_direct<T, SYM, DOT>(a, r0 + ns, nrows - ns, warp, CW, lane));
+    }
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(empty + s);
+  }
+  if (DOT)
+    grid_dd_reduce(dot, threadIdx.x, CW * 32, 2, s_warp, a.partials, a.partials_len, a.counter, a.dot_out);
+}
+
+
 // resident CTAs per SM the register allocation must allow (only the warp-private walk asks: its two
 // tiles in flight per warp would otherwise take ~94 registers and a single CTA per SM)
 __host__ __device__ constexpr int pipe_min_ctas(bool sym, int walk, int cw)
@@ -825,7 +960,7 @@ __host__ __device__ constexpr int pipe_min_ctas(bool sym, int walk, int cw)
 }
 
 template <typename T, bool SYM, bool DOT, bool LONG, int CW, int WALK>
-__global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) spmv_pipe_kernel(const SpmvArgs<T> a)
+__global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) spmv_irr_kernel(const SpmvArgs<T> a)
 {
   constexpr bool SEGW = !SYM && walk_is_seg(WALK); // warp-private pipelined walk (general storage only)
   constexpr bool SPLIT = !SYM && WALK == WALK_SPLIT; // products and sums on different warps
@@ -855,7 +990,15 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
   __syncthreads();
 
   const int span = a.num_tiles - a.tile0;
-  const int my_tiles = ((int)blockIdx.x < span) ? (span - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  int my_tiles = ((int)blockIdx.x < span) ? (span - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // tiles of this CTA: b, b + grid, ... (default) or, SPLIT with flag bit 1, one contiguous run of tiles
+  int tile_first = a.tile0 + blockIdx.x, tile_step = gridDim.x;
+  if (SPLIT && (a.flags & 2)) {
+    const int base = span / (int)gridDim.x, rem = span % (int)gridDim.x;
+    my_tiles = base + ((int)blockIdx.x < rem ? 1 : 0);
+    tile_first = a.tile0 + (int)blockIdx.x * base + min((int)blockIdx.x, rem);
+    tile_step = 1;
+  }
 
   if (warp == CW) {
     if (lane == 0) {
@@ -878,17 +1021,17 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
       int2 n0 = make_int2(0, 0), n1 = make_int2(0, 0);
       constexpr bool PREFETCH = SEGW || SPLIT;
       if (PREFETCH && my_tiles > 0) {
-        n0 = __ldg(tmeta + a.tile0 + blockIdx.x);
-        n1 = __ldg(tmeta + a.tile0 + blockIdx.x + 1);
+        n0 = __ldg(tmeta + tile_first);
+        n1 = __ldg(tmeta + tile_first + 1);
       }
       for (int it = 0, s = 0, use = 0; it < my_tiles; ++it, s = (s + 1 == stages ? 0 : s + 1), use += (s == 0)) {
-        const int tile = a.tile0 + blockIdx.x + it * gridDim.x;
+        const int tile = tile_first + it * tile_step;
         int2 t0, t1;
         if constexpr (SEGW || SPLIT) {
           t0 = n0, t1 = n1;
           if (it + 1 < my_tiles) {
-            n0 = __ldg(tmeta + tile + gridDim.x);
-            n1 = __ldg(tmeta + tile + gridDim.x + 1);
+            n0 = __ldg(tmeta + tile + tile_step);
+            n1 = __ldg(tmeta + tile + tile_step + 1);
           }
         }
         if (use > 0)
@@ -1264,9 +1407,12 @@ static int env_int(const char* name, int dflt)
   return (v && *v) ? std::atoi(v) : dflt;
 }
 
+static bool plan_walk_is_irr(const Plan& p) { return !p.symmetric && (walk_is_seg(p.walk) || p.walk == WALK_SPLIT); }
 static size_t pipe_smem_bytes(const Plan& p)
 {
-  return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 24 * p.stages + 8 * 64;
+  if (plan_walk_is_irr(p)) // spmv_irr_kernel: a third barrier per stage, more reduction scratch
+    return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 24 * p.stages + 8 * 64;
+  return (size_t)p.stages * (p.stage_bytes + sizeof(StageMeta)) + 16 * p.stages + 8 * 32;
 }
 
 static int plan_partition(Plan* p, const int32_t* d_rowptr, cudaStream_t st)
@@ -1327,7 +1473,7 @@ static void plan_choose_walk(Plan* p)
   }
   const double mean = p->rows > 0 ? (double)p->nnz / (double)p->rows : 0.0;
   if (p->max_row_len > SHORT_ROW && (double)p->max_row_len > 16.0 * mean)
-    p->walk = WALK_STREAM;
+    p->walk = p->symmetric ? WALK_STREAM : WALK_SPLIT; // general: 0.165 -> 0.139 ms on the 3 M-row power-law matrix
   else if (p->symmetric)
     p->walk = mean <= 4.0 ? WALK_ROW4 : WALK_ROW8;
   else
@@ -1425,10 +1571,16 @@ static int launch_pipe(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st)
 {
   const size_t smem = pipe_smem_bytes(p);
   static SmemCache cache;
-  if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK>, smem, cache))
-    return rc;
   const int grid = std::min<long long>(a.num_tiles - a.tile0, (long long)num_sms() * p.ctas_per_sm);
-  spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK><<<grid, (CW + 1) * 32, smem, st>>>(a);
+  if constexpr (!SYM && (walk_is_seg(WALK) || WALK == WALK_SPLIT)) {
+    if (int rc = set_smem(spmv_irr_kernel<T, SYM, DOT, LONG, CW, WALK>, smem, cache))
+      return rc;
+    spmv_irr_kernel<T, SYM, DOT, LONG, CW, WALK><<<grid, (CW + 1) * 32, smem, st>>>(a);
+  } else {
+    if (int rc = set_smem(spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK>, smem, cache))
+      return rc;
+    spmv_pipe_kernel<T, SYM, DOT, LONG, CW, WALK><<<grid, (CW + 1) * 32, smem, st>>>(a);
+  }
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -1585,7 +1737,8 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   a.warp_rows = p.d_warp_rows;
   {
     static const int seg_ef = env_int("B200_SPMV_SEG_EVICT_FIRST", 0);
-    a.flags = seg_ef ? 1 : 0;
+    static const int contig = env_int("B200_SPMV_TILE_CONTIG", 0);
+    a.flags = (seg_ef ? 1 : 0) | (contig ? 2 : 0);
   }
   a.tile0 = ranged ? tile_begin : 0;
   a.num_tiles = ranged ? tile_end : p.num_tiles;

@@ -50,3 +50,33 @@ def test_argument_checks():
     L = spmv_b200.lib()
     assert L.b200_csr_plan_create(None, 1, 1, 0, None, 0, None) == -1
     assert L.b200_gather_f64(-1, None, None, None, None) == -1
+
+
+def test_register_budget_of_the_tuned_kernels():
+    """ptxas' allocation for the pipeline kernels decides how many CTAs an SM holds, and it is fragile: unrelated
+    edits to the kernel once took the 27-point walk from 96 to 120 registers (one resident CTA instead of two,
+    0.85 -> 1.42 ms).  Budgets = 65536 registers / (threads per CTA x CTAs per SM of plan_default_shape)."""
+    import os
+    import re
+    import subprocess
+    log = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "build", "kernels", "spmv_csr.ptxas.log")
+    if not os.path.exists(log):
+        pytest.skip("no ptxas log (libraries were prebuilt elsewhere)")
+    blocks = re.split(r"ptxas info\s+: Compiling entry function '([^']+)' for 'sm_100a'", open(log).read())
+    regs = {}
+    for i in range(1, len(blocks), 2):
+        name = subprocess.run(["c++filt", blocks[i]], capture_output=True, text=True).stdout.strip()
+        m = re.search(r"Used (\d+) registers", blocks[i + 1])
+        regs[re.sub(r"\(.*", "", name).replace("void b200::", "")] = int(m.group(1))
+    budget = {  # kernel: (threads per CTA, CTAs per SM)
+        "spmv_pipe_kernel<double, false, false, false, 8, 0>": (288, 2),   # general 27-point (16-entry walk)
+        "spmv_pipe_kernel<double, false, true, false, 8, 0>": (288, 2),    # ... with the p.Ap epilogue
+        "spmv_pipe_kernel<double, false, false, false, 8, 4>": (288, 4),   # general 7-point (8-entry single chunk)
+        "spmv_pipe_kernel<double, true, false, false, 16, 5>": (544, 2),   # symmetric 7-point (4-entry single chunk)
+        "spmv_pipe_kernel<double, true, false, false, 8, 2>": (288, 3),    # symmetric 27-point (8-entry walk)
+        "spmv_irr_kernel<double, false, false, false, 16, 8>": (544, 2),   # split stream walk (power-law rows)
+    }
+    for k, (threads, ctas) in budget.items():
+        assert k in regs, k
+        alloc = (regs[k] + 7) // 8 * 8  # registers are allocated in units of 8 per thread
+        assert alloc * threads * ctas <= 65536, (k, regs[k])

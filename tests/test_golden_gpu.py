@@ -191,3 +191,74 @@ def test_cg_bit_identical_to_reference_64cubed(ex):
     it8_o, x8_o, hist8_o = OCG.cg(mult, b_h, 5000, 1e-8)
     assert it8 == it8_o and np.array_equal(hist8, hist8_o) and np.array_equal(x.cpu().numpy(), x8_o)
     A.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# The CG driver's execution modes -- separate vector kernels / one fused cooperative step, stream /
+# captured CUDA graph of 8 iterations, p.Ap in the SpMV epilogue or not -- are the same algorithm: same
+# iteration count, same residual history and x, bit for bit (general storage, stencil rows), whatever
+# kmax is relative to the graph length.  B200_CG_GRAPH_STRICT turns a capture failure into an error
+# instead of a silent fall-back to the stream path.
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("graph,fused_vec,fused_dot", [(0, 0, 1), (0, 1, 1), (1, 0, 1), (1, 1, 1), (1, 1, 0), (1, 0, 0)])
+def test_cg_modes_agree(ex, graph, fused_vec, fused_dot, monkeypatch):
+    from oracle import cg as OCG
+    from oracle import kernels as OK
+    from spmv_b200 import synth
+    n1 = 20
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    rp32, c32 = rp.astype(np.int32), col.astype(np.int32)
+    mult = lambda p: OK.spmv(rp32, c32, val, p)  # noqa: E731
+    b_h = mult(np.ones(N))
+    monkeypatch.setenv("B200_CG_GRAPH", str(graph))
+    monkeypatch.setenv("B200_CG_GRAPH_STRICT", "1")
+    monkeypatch.setenv("B200_CG_FUSED_VEC", str(fused_vec))
+    monkeypatch.setenv("B200_CG_FUSED_DOT", str(fused_dot))
+    A = api.Matrix.create_matrix(ex, rp32, c32, val, N, N, [], [], False, api.P2P_BLOCKING)
+    b = torch.from_numpy(b_h).cuda()
+    x = torch.zeros(N, dtype=torch.float64, device="cuda")
+    for kmax, rtol in ((1, 1e-30), (7, 1e-30), (8, 1e-30), (21, 1e-30), (500, 1e-10), (3, 1e-30)):
+        it_o, x_o, hist_o = OCG.cg(mult, b_h, kmax, rtol)
+        x.fill_(float("nan"))
+        it, hist = api.cg(ex, A, b, x, kmax, rtol, history=True)
+        assert it == it_o, (kmax, it, it_o)
+        assert np.array_equal(hist, hist_o), kmax
+        assert np.array_equal(x.cpu().numpy(), x_o), kmax
+    it, ph = api.cg_phases(ex, A, b, x, 12, 1e-30)  # profile mode: same count, sane timings
+    assert it == 12 and ph["local"] > 0 and ph["vector"] > 0
+    A.close()
+    # a second operator at the same address range must not replay the first one's graph
+    A2 = api.Matrix.create_matrix(ex, rp32, c32, 2.0 * val, N, N, [], [], False, api.P2P_BLOCKING)
+    it2, hist2 = api.cg(ex, A2, b, x, 500, 1e-10, history=True)
+    it2_o, x2_o, hist2_o = OCG.cg(lambda p: OK.spmv(rp32, c32, 2.0 * val, p), b_h, 500, 1e-10)
+    assert it2 == it2_o and np.array_equal(hist2, hist2_o) and np.array_equal(x.cpu().numpy(), x2_o)
+    A2.close()
+
+
+def test_cg_symmetric_modes(ex, monkeypatch):
+    """Symmetric storage (two kernels per SpMV, scatter adds) through the graph + fused step: same iteration
+    count as the stream path and the oracle (+-1), history within 1e-10 over the first 20 iterations."""
+    from oracle import cg as OCG
+    from oracle import kernels as OK
+    from spmv_b200 import synth
+    n1 = 16
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 7)
+    rp32, c32 = rp.astype(np.int32), col.astype(np.int32)
+    mult = lambda p: OK.spmv(rp32, c32, val, p)  # noqa: E731
+    b_h = mult(np.ones(N))
+    it_o, x_o, hist_o = OCG.cg(mult, b_h, 500, 1e-10)
+    A = api.Matrix.create_matrix(ex, rp32, c32, val, N, N, [], [], True, api.P2P_BLOCKING)
+    b = torch.from_numpy(b_h).cuda()
+    x = torch.zeros(N, dtype=torch.float64, device="cuda")
+    monkeypatch.setenv("B200_CG_GRAPH_STRICT", "1")
+    for graph, fv in ((0, 0), (1, 1), (1, 0), (0, 1)):
+        monkeypatch.setenv("B200_CG_GRAPH", str(graph))
+        monkeypatch.setenv("B200_CG_FUSED_VEC", str(fv))
+        it, hist = api.cg(ex, A, b, x, 500, 1e-10, history=True)
+        assert abs(it - it_o) <= 1
+        m = min(20, it, it_o)
+        assert np.max(np.abs(hist[:m] - hist_o[:m]) / hist_o[:m]) < TOL_HIST
+        assert rel_l2(x.cpu().numpy(), x_o) < 1e-9
+    A.close()
