@@ -24,7 +24,6 @@ sys.path.insert(0, ROOT)
 
 NX = NY = 256
 NZ_PER_GPU = 256
-CPU_SAMPLE_NZ = 64  # planes of the CPU legs' slab (1/4 of the 1-GPU workload)
 CONFIG5_ROWS_PER_GPU = 6_250_000  # BASELINE configs[4]: ~50 M rows on 8 GPUs
 
 
@@ -38,10 +37,9 @@ def parse():
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling (BASELINE configs[2]): the 256^3 grid split over the GPUs, nz = 256 / N")
     ap.add_argument("--no-extras", action="store_true", help="skip the 'also' measurements and cpu_baseline")
-    ap.add_argument("--with-cusparse", action="store_true",
-                    help="N=1 only: also time cusparseSpMV (through torch.sparse CSR) on the 27-point operator -- "
-                         "what the reference's CUDA backend runs (cuda/csr_kernels.cuda.cu:106-151); context, not a leg "
-                         "of the contract")
+    ap.add_argument("--no-library-context", action="store_true",
+                    help="N=1: skip the cuSPARSE SpMV / cuBLAS BLAS-1 context timings (what the reference's CUDA backend "
+                         "runs, cuda/csr_kernels.cuda.cu:106-151, cuda/cg.cuda.cu:88-150); library code, context only")
     ap.add_argument("--config5-rows", type=int, default=CONFIG5_ROWS_PER_GPU,
                     help="rows per GPU of the power-law / PETSc leg (default 6.25 M = 50 M rows at 8 GPUs; 0 skips it)")
     return ap.parse_args()
@@ -375,6 +373,71 @@ def measure_config5(api, ex, dev, rank, size, timer, peak, rows_per_gpu):
     return out
 
 
+def measure_config1(api, ex, dev, rank, size, timer, n=1_000_000, n_apply=100):
+    """BASELINE configs[0] as the reference's driver runs it (demos/spmv.cpp:73-108) on create_A(N)
+    (demos/CreateA.cpp:31-103): warm-up, then n_apply x {L2GMap::update; Matrix::mult; x <- y}, final ||x||_2.
+    24 MB of matrix: a latency-bound case -- what is reported is us per step and what it is made of.
+    Parity: the same 100 products recomputed on the host in numpy, row sums left to right (the operator is
+    tridiagonal: three vector expressions); bit-identical at one rank, <= 1e-12 otherwise (a rank's ghost column
+    is numbered last, so its boundary row adds in another order)."""
+    import numpy as np
+    import torch
+    from spmv_b200 import synth
+    A = api.create_A(n, ex)
+    cm = A.col_map()
+    M, r0 = A.rows(), cm.global_offset()
+    x = torch.zeros(M + cm.num_ghosts(), dtype=torch.float64, device=dev)
+    x[:M] = torch.from_numpy(synth.bump_vector(n, r0, r0 + M)).to(dev)
+    y = torch.empty(M, dtype=torch.float64, device=dev)
+    cm.update(x)  # warm-up (demos/spmv.cpp:81-82)
+    A.mult(x, y)
+    y_first = y.cpu().numpy()
+
+    def step(_i):
+        cm.update(x)
+        A.mult(x, y)
+        x[:M].copy_(y)
+
+    ms = timer.run(step, n_apply)
+    g = 0.1
+
+    def apply(v):  # rows [g, 1-2g, g], first [1-g, g], last [g, 1-g]; sums left to right like csr_kernels.cpp:45-47
+        out = np.empty_like(v)
+        out[1:-1] = (g * v[:-2] + (1.0 - 2.0 * g) * v[1:-1]) + g * v[2:]
+        out[0] = (1.0 - g) * v[0] + g * v[1]
+        out[-1] = g * v[-2] + (1.0 - g) * v[-1]
+        return out
+
+    xg = synth.bump_vector(n, 0, n)
+    want_first = apply(xg)[r0:r0 + M]
+    for _ in range(n_apply):
+        xg = apply(xg)
+    got = x[:M].cpu().numpy()
+    want = xg[r0:r0 + M]
+    e = torch.tensor([float(np.sum((got - want) ** 2)), float(np.sum(want ** 2)), float(np.sum(got ** 2)),
+                      float(np.sum((y_first - want_first) ** 2)), float(np.sum(want_first ** 2))], dtype=torch.float64, device=dev)
+    if size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(e)
+    rel = float(torch.sqrt(e[0] / e[1]).item())
+    rel_first = float(torch.sqrt(e[3] / e[4]).item())
+    if not (rel <= 1e-12 and rel_first <= 1e-12):
+        raise RuntimeError(f"config 1: x after {n_apply} products differs from the host recomputation ({rel}, first y {rel_first})")
+    info = A._info()
+    nbytes = bytes_general(n * 3 - 2, 0, n, n, False)
+    out = {"rows_global": n, "n_apply": n_apply, "us_per_step": ms / n_apply * 1e3, "GBps": nbytes / (ms / n_apply * 1e-3) / 1e9,
+           "final_x_norm": float(torch.sqrt(e[2]).item()), "final_x_norm_host": float(np.linalg.norm(xg)),
+           "parity": {"rel_l2_final_x": rel, "rel_l2_first_y": rel_first,
+                      "bit_identical": bool(size == 1 and np.array_equal(got, want) and np.array_equal(y_first, want_first)),
+                      "tolerance": 1e-12, "how": "100 products recomputed on the host, left-to-right row sums"},
+           "halo_mode": cm.halo_mode(), "launches_per_step": 2 + (2 if size > 1 else 0),
+           "bound": "latency: 12 MB of matrix per GPU stream in ~3 us; a step is 2-4 kernel launches + one device copy "
+                    "(+ the neighbour's flag over NVLink), not bandwidth",
+           "local_nnz": int(info[6])}
+    A.close()
+    return out
+
+
 def measure_cg(api, op, timer, dev, size):
     """CG on `op` (b = A*1, x0 = 0): iterations/s over a fixed 100 iterations, then the solve
     to rtol 1e-8 (BASELINE config 3: kmax 5000) with its iteration count and final residual."""
@@ -389,9 +452,24 @@ def measure_cg(api, op, timer, dev, size):
     api.cg(op.ex, op.A, b, xs, 10, 0.0)  # warm-up
     iters = 100
     ms = timer.run(lambda i: api.cg(op.ex, op.A, b, xs, iters, 0.0), 1)
-    res = {"iters_per_s": iters / (ms * 1e-3), "ms_per_iter": ms / iters, "rows_per_gpu": M,
+    ms2 = timer.run(lambda i: api.cg(op.ex, op.A, b, xs, iters, 0.0), 1)  # second call: the figure must reproduce
+    # per-phase device time (profile mode: no graph, one iteration at a time, CUDA events between the parts)
+    _, ph = api.cg_phases(op.ex, op.A, b, xs, 20, 0.0)
+    pht = torch.tensor([ph["update"], ph["local"], ph["remote"], ph["vector"]], dtype=torch.float64, device=dev)
+    if size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(pht, op=dist.ReduceOp.MAX)
+    ph = dict(zip(("halo_update_us", "local_spmv_us", "halo_wait_and_remote_spmv_us", "vector_step_and_allreduces_us"),
+                  [float(v) for v in pht.tolist()]))
+    ph["sum_us"] = sum(ph.values())
+    ph["launch_gaps_and_skew_us"] = min(ms, ms2) / iters * 1e3 - ph["sum_us"]
+    ph["how"] = ("spmv::cg profile mode, max over ranks of the per-iteration mean; gaps = timed ms_per_iter (graph path) "
+                 "minus the sum: negative means the graph / overlap hides more than the profile mode's serial launches cost")
+    res = {"iters_per_s": iters / (min(ms, ms2) * 1e-3), "ms_per_iter": min(ms, ms2) / iters, "rows_per_gpu": M,
+           "ms_per_iter_runs": [ms / iters, ms2 / iters], "halo_mode": op.col_map.halo_mode(), "phases": ph,
            "algorithmic_GBps": (op.algorithmic_bytes() + 11 * 8 * M) * size / (ms / iters * 1e-3) / 1e9,
-           "note": "100 iterations through spmv::cg incl. its setup (allocations, r0 norm)"}
+           "note": "100 iterations through spmv::cg incl. its setup (r0 norm; the workspace and the captured graph are "
+                   "cached on the executor after the warm-up call), best of two calls"}
     holder = {}
 
     def solve(_i):
@@ -524,8 +602,12 @@ def run_b200(args):
         also["cg_sym_7pt"] = measure_cg(api, ops, timer, dev, size)
         ops.close()
         del ops
-        if args.with_cusparse and size == 1:
-            also["cusparse_general_27pt"] = measure_cusparse(dev, nz)
+        if size == 1 and not args.no_library_context:
+            # what the reference's CUDA backend would run on this GPU: cusparseSpMV + cuBLAS BLAS-1 (library code)
+            also["library_context"] = {"cusparse_general_27pt": measure_cusparse(dev, nz),
+                                       "cublas_cg_vector_ops": measure_cublas_blas1(dev, NX * NY * nz)}
+        # ---- config 1: the reference's own demo loop on create_A(1e6) --------------------------
+        also["config1_createA"] = measure_config1(api, ex, dev, rank, size, timer)
         # ---- config 5: power-law rows through the PETSc reader --------------------------
         if args.config5_rows > 0:
             also["powerlaw_petsc"] = measure_config5(api, ex, dev, rank, size, timer, peak, args.config5_rows)
@@ -582,6 +664,55 @@ def measure_cusparse(dev, nz, steps=20, warmup=3):
         return {"error": str(e)[:200]}
 
 
+def measure_cublas_blas1(dev, m, iters=20):
+    """The vector half of one iteration of the reference's CUDA CG (cuda/cg.cuda.cu:88-150): cublasDdot x2,
+    cublasDaxpy x3, cublasDscal x1 with device pointer mode, on vectors of m doubles.  Library code, context
+    only: what this repo's three (or one fused) vector kernels replace."""
+    try:
+        import ctypes as C
+        import glob
+        import torch
+        cands = glob.glob(os.path.join(os.path.dirname(torch.__file__), "lib", "libcublas.so*")) \
+            + glob.glob(os.path.join(os.path.dirname(os.path.dirname(torch.__file__)), "nvidia", "cublas", "lib", "libcublas.so*")) \
+            + glob.glob("/usr/local/cuda/lib64/libcublas.so*")
+        if not cands:
+            return {"error": "libcublas not found"}
+        L = C.CDLL(sorted(cands)[0])
+        h = C.c_void_p()
+        assert L.cublasCreate_v2(C.byref(h)) == 0
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        assert L.cublasSetStream_v2(h, st) == 0
+        assert L.cublasSetPointerMode_v2(h, 1) == 0  # CUBLAS_POINTER_MODE_DEVICE (cg.cuda.cu:62-63)
+        p, ap, x, r = (torch.rand(m, dtype=torch.float64, device=dev) for _ in range(4))
+        sc = torch.tensor([1e-3, -1e-3, 0.5, 0.0, 0.0], dtype=torch.float64, device=dev)
+        P = lambda t, off=0: C.c_void_p(t.data_ptr() + 8 * off)  # noqa: E731
+        n, one = C.c_int(m), C.c_int(1)
+
+        def it():
+            L.cublasDdot_v2(h, n, P(p), one, P(ap), one, P(sc, 3))      # p.Ap        :109
+            L.cublasDaxpy_v2(h, n, P(sc, 0), P(p), one, P(x), one)       # x += a p    :126
+            L.cublasDaxpy_v2(h, n, P(sc, 1), P(ap), one, P(r), one)      # r -= a Ap   :121
+            L.cublasDdot_v2(h, n, P(r), one, P(r), one, P(sc, 4))        # r.r         :131
+            L.cublasDscal_v2(h, n, P(sc, 2), P(p), one)                  # p *= beta   :148
+            L.cublasDaxpy_v2(h, n, P(sc, 2), P(r), one, P(p), one)       # p += r      :150
+
+        for _ in range(3):
+            it()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            it()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        L.cublasDestroy_v2(h)
+        return {"ms_per_iteration": ms, "vector_passes": 14, "GBps": 14 * 8 * m / ms / 1e6,
+                "how": "cublasDdot x2 + cublasDaxpy x3 + cublasDscal x1, device pointer mode, 6 library launches"}
+    except Exception as e:  # context measurement: never fail the bench over it
+        return {"error": f"{type(e).__name__}: {e}"[:200]}
+
+
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
 # (profiles/): filled in when a capture of the current kernel exists, else null.
 TRAFFIC_NCU = {"sym7": 1072455000 + 106979584}  # profiles/r01_sym7_final_ncu_summary.txt (ncu flushes L2 before
@@ -589,87 +720,40 @@ TRAFFIC_NCU = {"sym7": 1072455000 + 106979584}  # profiles/r01_sym7_final_ncu_su
 
 
 # ----------------------------------------------------------------------------
-# CPU legs: the reference's own OpenMP kernel (oracle/_ref), all host threads, on a slab of
-# the same operator (symmetric-storage 7-point)
+# CPU legs (bench_cpu_legs.py): the reference's own CPU implementation of the path on the box's host cores.
+# cpu_baseline / --impl reference = its OpenMP kernel on the FULL headline operator (symmetric-storage
+# 7-point 256^3, same config as the GPU arm); `legs` carries the CPU twin of every GPU leg in `also`.
 # ----------------------------------------------------------------------------
-def _split_lower(rp, col, val, rows):
-    """Strictly-lower triangle + diagonal of a square block with sorted rows (Matrix.cpp:337-349)."""
-    import numpy as np
-    r = np.repeat(np.arange(rows, dtype=np.int64), np.diff(rp))
-    low = col < r
-    diag = np.zeros(rows)
-    d = col == r
-    diag[r[d]] = val[d]
-    rp_l = np.zeros(rows + 1, dtype=np.int64)
-    np.cumsum(np.bincount(r[low], minlength=rows), out=rp_l[1:])
-    return rp_l.astype(np.int32), col[low].astype(np.int32), val[low].copy(), diag
+CPU_WORKLOAD = (f"BASELINE configs[1]: symmetric-storage fp64 CSR SpMV, 3-D 7-point Laplacian {NX}x{NY}x{NZ_PER_GPU} "
+                "(the whole 1-GPU workload); each step = one SpMV of the reference's CPU kernel")
 
 
-def _cpu_operator(sample_nz):
-    import numpy as np
-    from oracle import kernels as OK
-    from spmv_b200 import synth
-    rp, col, val = synth.laplace3d_rows(NX, NY, sample_nz, 0, sample_nz, 7)
-    rows = len(rp) - 1
-    rp_l, ci_l, v_l, diag = _split_lower(rp, col, val, rows)
-    cores = os.cpu_count() or 1
-    if OK.have_ref():
-        op = OK.RefOmp(rows, rows, rp_l, ci_l, v_l, diagonal=diag, symmetric=True, threads=cores)
-        kind = "reference"
-        run = lambda x, y: op.run(x, y)  # noqa: E731
-    else:  # the plain-C port, one thread
-        kind, cores = "port", 1
-
-        def run(x, y):
-            y[:] = OK.symv(rp_l, ci_l, v_l, diag, x)
-    x = synth.bump_vector(rows, 0, rows)
-    y = np.zeros(rows)
-    nbytes = bytes_symmetric(len(v_l), 0, rows, 0)
-    return run, x, y, nbytes, kind, cores, rows
-
-
-def _cpu_sample_text(rows, kind, cores, n):
-    return (f"symmetric-storage 7-point Laplacian {NX}x{NY}x{CPU_SAMPLE_NZ} slab ({rows} rows, "
-            f"1/{NZ_PER_GPU // CPU_SAMPLE_NZ} of the 1-GPU workload; GB/s is size-independent), {n} SpMVs, "
-            + (f"reference openmp/csr_kernels.openmp.cpp symmetric kernel, OMP_NUM_THREADS={cores}"
-               if kind == "reference" else "oracle C port, 1 thread"))
-
-
-def cpu_baseline(budget_s=12.0):
-    run, x, y, nbytes, kind, cores, rows = _cpu_operator(CPU_SAMPLE_NZ)
-    run(x, y)
-    t0, n = time.perf_counter(), 0
-    while True:
-        run(x, y)
-        n += 1
-        dt = time.perf_counter() - t0
-        if dt > budget_s or n >= 300:
-            break
-    return {"value": nbytes * n / dt / 1e9, "unit": "GB/s", "cores": cores, "kind": kind,
-            "ms_per_spmv": dt / n * 1e3, "sample": _cpu_sample_text(rows, kind, cores, n)}
+def cpu_baseline(budget_s=8.0, with_legs=True):
+    import bench_cpu_legs as CL
+    h = CL.omp_spmv(7, True, nz=NZ_PER_GPU, budget_s=budget_s)
+    out = {"value": h["GBps"], "unit": "GB/s", "cores": h["cores"], "kind": h["kind"], "ms_per_spmv": h["ms_per_spmv"],
+           "GFLOPs": h["GFLOPs"], "same_config": True,
+           "sample": f"{h['what']}; {h['spmvs_timed']} SpMVs of the full operator ({h['rows']} rows)"}
+    if with_legs:
+        out["legs"] = CL.all_legs()
+    return out
 
 
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    run, x, y, nbytes, kind, cores, rows = _cpu_operator(CPU_SAMPLE_NZ)
-    for _ in range(max(args.warmup, 1)):
-        run(x, y)
-    steps = min(args.steps, 100)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        run(x, y)
-    dt = time.perf_counter() - t0
-    v = nbytes * steps / dt / 1e9
+    import bench_cpu_legs as CL
+    steps = max(1, min(args.steps, 200))
+    h = CL.omp_spmv(7, True, nz=NZ_PER_GPU, steps=steps)
+    v = h["GBps"]
     print(json.dumps({
         "impl": "reference", "metric": "spmv_algorithmic_GBps", "value": v, "unit": "GB/s", "n_gpus": args.gpus,
-        "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True,
+        "steps": steps, "warmup": 1, "ms_per_step": h["ms_per_spmv"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "BASELINE configs[1]: symmetric-storage fp64 CSR SpMV, 3-D 7-point Laplacian; each step = "
-                               "one SpMV of the reference's CPU kernel on a bounded slab of the operator",
-                   "rows": rows},
-        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cores, "kind": kind,
-                         "sample": _cpu_sample_text(rows, kind, cores, steps)},
+        "config": {"workload": CPU_WORKLOAD, "rows": h["rows"], "stored_nnz": h["stored_nnz"], "same_config_as_gpu_arm": True},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": h["cores"], "kind": h["kind"],
+                         "sample": f"{h['what']}; {steps} SpMVs of the full operator",
+                         "legs": CL.all_legs() if not args.no_extras else None},
         "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 

@@ -15,6 +15,7 @@ Legs (all on the workloads bench.py's GPU legs run, sizes stated in each record)
   cg27_mpi      the reference's cg.cpp:21-98 at R thread-ranks on a 256x256xZ slab of the 27-point operator
                                                                <-> also.cg_27pt
   cg_sym7_mpi   same on the symmetric-storage 7-point operator  <-> also.cg_sym_7pt
+  config1_mpi   BASELINE configs[0] itself: demos/spmv.cpp loop on create_A(1e6) at 2 thread-ranks   <-> also.config1
   powerlaw_omp  reference OpenMP kernel, general storage, power-law rows (3 M-row twin of config 5)
                                                                <-> also.powerlaw_petsc
 """
@@ -181,6 +182,37 @@ def mpi_cg(stencil, symmetric, nz=64, iters=20):
                     f"{'symmetric' if symmetric else 'general'} storage"}
 
 
+def config1_mpi(n=1_000_000, ranks=2, n_apply=100):
+    """BASELINE configs[0] as written: demos/spmv.cpp:73-108 on create_A(N) (demos/CreateA.cpp:31-103), general
+    CSR, pure MPI at 2 ranks (thread-ranks here), ReferenceExecutor, collective_blocking."""
+    from oracle import ref_api as R
+    from spmv_b200 import synth
+    if not R.available():
+        return {"unavailable": "oracle/_ref/libspmv_ref.so not built"}
+    out = {}
+
+    def body(rank):
+        A = R.RefMatrix.create_A(n)
+        pl = A.plan(0)
+        r0, m = pl["global_offset"], pl["local_size"]
+        x = np.zeros(m + pl["num_ghosts"])
+        x[:m] = synth.bump_vector(n, r0, r0 + m)
+        y = np.zeros(m)
+        t, nrm = A.demo_spmv_loop(x, y, n_apply)
+        out[rank] = (t, nrm, A.info()["local_nnz"])
+        A.close()
+
+    R.run_ranks(ranks, body)
+    t = {k: max(o[0][k] for o in out.values()) / n_apply for k in ("update", "mult", "copy")}
+    nnz = sum(o[2] for o in out.values())
+    step = t["update"] + t["mult"] + t["copy"]
+    return {"ranks": ranks, "cores": cores(), "kind": "reference", "us_update_max": t["update"] * 1e6,
+            "us_mult_max": t["mult"] * 1e6, "us_copy_max": t["copy"] * 1e6, "us_per_step": step * 1e6,
+            "GBps": bytes_general(nnz, n, n) / (t["update"] + t["mult"]) / 1e9, "final_x_norm": out[0][1], "n_apply": n_apply,
+            "rows": n, "what": f"demos/spmv.cpp loop on create_A({n}), {ranks} thread-ranks, reference L2GMap::update "
+                               "(collective_blocking) + sequential csr_kernels.cpp + copy, max over ranks per phase"}
+
+
 def powerlaw_omp(rows=3_000_000, budget_s=4.0):
     from oracle import kernels as OK
     from spmv_b200 import api, synth
@@ -203,7 +235,8 @@ def powerlaw_omp(rows=3_000_000, budget_s=4.0):
 def all_legs(light=False):
     """Every CPU twin of the GPU legs; each leg is bounded to a few seconds of timed work."""
     legs = {}
-    for name, fn in (("general27_omp", lambda: omp_spmv(27, False, nz=64 if light else 256, budget_s=4.0)),
+    for name, fn in (("config1_mpi", lambda: config1_mpi(100_000 if light else 1_000_000)),
+                     ("general27_omp", lambda: omp_spmv(27, False, nz=64 if light else 256, budget_s=4.0)),
                      ("mpi_sym7", lambda: mpi_spmv(7, True, nz=64 if light else 256, n_apply=10 if light else 20)),
                      ("cg27_mpi", lambda: mpi_cg(27, False, nz=32 if light else 64, iters=10 if light else 20)),
                      ("cg_sym7_mpi", lambda: mpi_cg(7, True, nz=32 if light else 64, iters=10 if light else 20)),

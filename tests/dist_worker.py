@@ -334,6 +334,54 @@ def main():
         check(cases.same_plan(A.col_map().plan(), got["plan"]), "create_A: plan differs")
         check(cases.same_block(A.local_block(), got["local"]), "create_A: block differs")
     A.close()
+    # BASELINE configs[0] as written: demos/spmv.cpp:73-108 on create_A(1 000 000) -- warm-up, 100 x {update; mult;
+    # x <- y}, final ||x||_2 -- against the reference's own loop at the same number of thread-ranks: halo lists and
+    # block bit-exact, the first y and the x after 100 products bit-identical (3-entry rows, one thread per row in
+    # the reference's order; every rank sums its rows in the same local-column order as the reference's rank does)
+    if mode == "gpu":
+        n1 = 1_000_000
+        A = api.create_A(n1, ex)
+        cmap = A.col_map()
+        m, r0 = A.rows(), cmap.global_offset()
+        x = torch.zeros(m + cmap.num_ghosts(), dtype=torch.float64, device=dev)
+        x[:m] = torch.from_numpy(synth.bump_vector(n1, r0, r0 + m)).to(dev)
+        y = torch.empty(m, dtype=torch.float64, device=dev)
+        cmap.update(x)
+        A.mult(x, y)
+        y_first = y.cpu().numpy()
+        for _ in range(100):
+            cmap.update(x)
+            A.mult(x, y)
+            x[:m].copy_(y)
+        ex.synchronize()
+        sq = (x[:m] * x[:m]).sum().reshape(1)
+        dist.all_reduce(sq)
+        if have_ref:
+            got = {}
+
+            def body3(r):
+                M = R.RefMatrix.create_A(n1)
+                pl = M.plan(0)
+                mm, rr0 = pl["local_size"], pl["global_offset"]
+                xr = np.zeros(mm + pl["num_ghosts"])
+                xr[:mm] = synth.bump_vector(n1, rr0, rr0 + mm)
+                yr = np.zeros(mm)
+                M.update(xr)
+                M.mult(xr, yr)
+                y0 = yr.copy()
+                _, nrm = M.demo_spmv_loop(xr, yr, 100)
+                if r == rank:
+                    got.update(plan=pl, local=M.block(0), y0=y0, x=xr[:mm].copy(), norm=nrm)
+                M.close()
+
+            R.run_ranks(size, body3)
+            check(cases.same_plan(cmap.plan(), got["plan"]), "config 1: halo plan differs")
+            check(cases.same_block(A.local_block(), got["local"]), "config 1: block differs")
+            check(np.array_equal(y_first, got["y0"]), "config 1: first y not bit-identical")
+            check(np.array_equal(x[:m].cpu().numpy(), got["x"]), "config 1: x after 100 products not bit-identical")
+            nrm = float(sq.sqrt().item())
+            check(abs(nrm - got["norm"]) <= 1e-12 * got["norm"], f"config 1: final norm {nrm} vs {got['norm']}")
+        A.close()
     dist.barrier()
     if rank == 0 and os.path.exists(path):
         os.remove(path)
