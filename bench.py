@@ -224,7 +224,7 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
            "kernel_ms_median": kern[len(kern) // 2],
            "GBps": op.algorithmic_bytes() * op.size / (ms_step * 1e-3) / 1e9,
            "GFLOPs": 2 * op.nnz_full() * op.size / (ms_step * 1e-3) / 1e9,
-           "kernel_GBps": op.local_kernel_bytes() / (kern_avg * 1e-3) / 1e9}
+           "kernel_GBps": op.local_kernel_bytes() / (kern_avg * 1e-3) / 1e9, "local_kernel_bytes": op.local_kernel_bytes()}
     out["frac_of_hbm_peak"] = out["kernel_GBps"] / peak
     if with_e2e:
         # host buffers: H2D of x and D2H of y inside the timed region.  Matrix::mult_host is
@@ -501,6 +501,37 @@ def measure_cg(api, op, timer, dev, size):
     return res
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def _bind_by_topo(idx):
+    """sysfs has no NUMA node for the GPU (containers often hide it): take the CPU affinity column of
+    `nvidia-smi topo -m` instead (first numeric range list on the GPU's row)."""
+    import re
+    try:
+        out = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+    except Exception as e:
+        return f"numa: unbound (topo: {type(e).__name__})"
+    for line in out.splitlines():
+        tok = re.split(r"\s+", re.sub(r"\x1b\[[0-9;]*m", "", line).strip())
+        if tok and tok[0] == f"GPU{idx}":
+            for t in tok[1:]:
+                if re.fullmatch(r"\d+(-\d+)?(,\d+(-\d+)?)*", t):
+                    cpus = _parse_cpulist(t) & os.sched_getaffinity(0)
+                    if not cpus:
+                        return f"numa: topo affinity {t} has no allowed cpus"
+                    if cpus == os.sched_getaffinity(0):
+                        return f"numa: topo affinity {t} = every allowed cpu (one socket visible)"
+                    os.sched_setaffinity(0, cpus)
+                    return f"numa: bound by nvidia-smi topo to cpus {t} ({len(cpus)} allowed)"
+    return "numa: unbound (no affinity column in nvidia-smi topo -m)"
+
+
 def bind_near_gpu(local_rank):
     """N > 1: run this rank (and first-touch its pinned buffers) on the CPUs of the NUMA node its
     GPU hangs off, so host<->device copies do not cross the socket link.  Returns a note for `config`."""
@@ -516,7 +547,7 @@ def bind_near_gpu(local_rank):
         with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
             node = int(f.read())
         if node < 0:
-            return "numa: single node"
+            return _bind_by_topo(idx)
         with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
             cpus = set()
             for part in f.read().strip().split(","):
@@ -621,12 +652,11 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "e2e": head["e2e"],
         "gpu_launches": head_launches, "clocks": clocks, "parity": head_parity,
         "roofline": {"bound": "hbm", "achieved": head["kernel_GBps"], "peak": peak, "unit": "GB/s",
-                     "frac": head["frac_of_hbm_peak"], "traffic": TRAFFIC_NCU.get("sym7"),
+                     "frac": head["frac_of_hbm_peak"], "traffic": ncu_traffic("sym7")[0], "traffic_source": ncu_traffic("sym7")[1],
                      "kernel": "spmv_pipe_kernel<double, SYM, ROW4S> (local block; the event pair also spans the "
                                "zero-fill of y, zero_fill_desc_kernel, that precedes it)",
                      "kernel_ms_avg": head["kernel_ms_avg"], "kernel_ms_min": head["kernel_ms_min"],
-                     "algorithmic_bytes": bytes_symmetric(cfg["stored_nnz_per_gpu"] if size == 1 else 0, 0,
-                                                          cfg["rows_per_gpu"], 0) if size == 1 else None,
+                     "algorithmic_bytes": head["local_kernel_bytes"],
                      "peak_source": peak_src, "frac_of_8TBps_nominal": head["kernel_GBps"] / 8000.0},
         "also": also,
     }
@@ -713,10 +743,20 @@ def measure_cublas_blas1(dev, m, iters=20):
         return {"error": f"{type(e).__name__}: {e}"[:200]}
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-# (profiles/): filled in when a capture of the current kernel exists, else null.
-TRAFFIC_NCU = {"sym7": 1072455000 + 106979584}  # profiles/r01_sym7_final_ncu_summary.txt (ncu flushes L2 before
-# each replay, so this is the cold-cache figure: in the bench loop part of y is still in L2 from the zero-fill kernel)
+def ncu_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the newest committed
+    profiles/r*_traffic.json (written by profiles/tools/ncu_summary.py --traffic-json from an `ncu --set full`
+    capture of this bench command); None when no capture of that kernel is on file."""
+    import glob
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), reverse=True):
+        try:
+            with open(f) as fh:
+                d = json.load(fh)
+            if key in d:
+                return d[key]["dram_bytes"], os.path.basename(f)
+        except Exception:
+            continue
+    return None, None
 
 
 # ----------------------------------------------------------------------------

@@ -23,6 +23,16 @@
 #include <mpi.h>
 #include <vector>
 
+// Where Eigen is installed the reference's own signatures (Matrix.h:40,47-48,55-56,96: Eigen::SparseMatrix<T,
+// RowMajor> blocks) are available too, so code written against the reference compiles unchanged; they convert to
+// HostCSR and delegate.  SPMV_NO_EIGEN switches them off.
+#if !defined(SPMV_NO_EIGEN) && defined(__has_include)
+#if __has_include(<Eigen/Sparse>)
+#include <Eigen/Sparse>
+#define SPMV_HAVE_EIGEN 1
+#endif
+#endif
+
 namespace spmv
 {
 
@@ -43,10 +53,60 @@ struct HostCSR {
   std::int64_t non_zeros() const { return static_cast<std::int64_t>(values.size()); }
 };
 
+#ifdef SPMV_HAVE_EIGEN
+/// Compressed row-major Eigen block -> HostCSR (outerIndexPtr / innerIndexPtr / valuePtr, csr_matrix.cpp:23-59).
+template <typename T>
+HostCSR<T> to_host_csr(const Eigen::SparseMatrix<T, Eigen::RowMajor>& m)
+{
+  HostCSR<T> h;
+  h.rows = static_cast<std::int32_t>(m.rows());
+  h.cols = static_cast<std::int32_t>(m.cols());
+  const auto nnz = static_cast<std::size_t>(m.nonZeros());
+  if (h.rows > 0)
+    h.rowptr.assign(m.outerIndexPtr(), m.outerIndexPtr() + h.rows + 1);
+  h.colind.assign(m.innerIndexPtr(), m.innerIndexPtr() + nnz);
+  h.values.assign(m.valuePtr(), m.valuePtr() + nnz);
+  return h;
+}
+#endif
+
 template <typename T>
 class SPMV_EXPORT Matrix
 {
 public:
+#ifdef SPMV_HAVE_EIGEN
+  using EigenBlock = Eigen::SparseMatrix<T, Eigen::RowMajor>;
+  /// The reference's three constructors (Matrix.h:40,47-48,55-56); blocks must be compressed.
+  Matrix(const EigenBlock& mat, std::shared_ptr<spmv::L2GMap> col_map, std::shared_ptr<spmv::L2GMap> row_map,
+         std::shared_ptr<DeviceExecutor> exec)
+      : Matrix(to_host_csr(mat), col_map, row_map, exec)
+  {
+  }
+  Matrix(const EigenBlock& mat_local, const EigenBlock& mat_remote, std::shared_ptr<spmv::L2GMap> col_map,
+         std::shared_ptr<spmv::L2GMap> row_map, std::shared_ptr<DeviceExecutor> exec)
+      : Matrix(to_host_csr(mat_local), to_host_csr(mat_remote), col_map, row_map, exec)
+  {
+  }
+  Matrix(const EigenBlock& mat_local, const EigenBlock& mat_remote,
+         const Eigen::Matrix<T, Eigen::Dynamic, 1>& mat_diagonal, std::shared_ptr<spmv::L2GMap> col_map,
+         std::shared_ptr<spmv::L2GMap> row_map, int nnz_full, std::shared_ptr<DeviceExecutor> exec)
+      : Matrix(to_host_csr(mat_local), to_host_csr(mat_remote),
+               std::vector<T>(mat_diagonal.data(), mat_diagonal.data() + mat_diagonal.size()), col_map, row_map, nnz_full,
+               exec)
+  {
+  }
+  /// Matrix.h:96: create_matrix from an Eigen block.
+  static Matrix<T>* create_matrix(MPI_Comm comm, std::shared_ptr<DeviceExecutor> exec, const EigenBlock& mat,
+                                  std::int64_t nrows_local, std::int64_t ncols_local,
+                                  std::vector<std::int64_t> row_ghosts, std::vector<std::int64_t> col_ghosts,
+                                  bool symmetric = false,
+                                  CommunicationModel cm = CommunicationModel::collective_blocking)
+  {
+    return create_matrix(comm, exec, to_host_csr(mat), nrows_local, ncols_local, std::move(row_ghosts),
+                         std::move(col_ghosts), symmetric, cm);
+  }
+
+#endif
   /// Single block; throws if the column map is overlapping (Matrix.cpp:28-29).
   Matrix(const HostCSR<T>& mat, std::shared_ptr<spmv::L2GMap> col_map,
          std::shared_ptr<spmv::L2GMap> row_map, std::shared_ptr<DeviceExecutor> exec);

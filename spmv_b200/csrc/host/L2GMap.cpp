@@ -453,6 +453,7 @@ void L2GMap::exchange_forward(T* vec_data, bool overlap) const
 template <typename T>
 void L2GMap::update(T* vec_data) const
 {
+  detail::NvtxRange r("halo:pack + exchange");
   exchange_forward(vec_data, overlapping());
 }
 //-----------------------------------------------------------------------------
@@ -461,6 +462,7 @@ void L2GMap::update_finalise(T*) const
 {
   if (!overlapping() || _neighbours.empty())
     return;
+  detail::NvtxRange r("halo:wait + unpack");
   const B200Executor* gpu = as_b200(_exec);
   if (gpu == nullptr)
     throw std::runtime_error("L2GMap::update_finalise needs the B200 executor");

@@ -6,6 +6,7 @@
 #include "L2GMap.h"
 #include "csr_matrix.h"
 #include "device_executor.h"
+#include "host_util.h"
 
 #include <atomic>
 #include <stdexcept>
@@ -182,27 +183,40 @@ void Matrix<T>::transpmult(const T*, T*) const
 template <typename T>
 void Matrix<T>::spmv(T* x, T* y) const
 {
+  detail::NvtxRange r("spmv:single block");
   _mat_local->mult(1, x, 0, y);
 }
 template <typename T>
 void Matrix<T>::spmv_overlap(T* x, T* y) const
 {
-  // local block runs while the halo values are in flight on the side stream
-  _mat_local->mult(1, x, 0, y);
+  // local block runs while the halo values are in flight
+  {
+    detail::NvtxRange r("spmv:local block");
+    _mat_local->mult(1, x, 0, y);
+  }
   _col_map->update_finalise(x);
+  detail::NvtxRange r("spmv:remote block");
   _mat_remote->mult(1, x, _mat_local->non_zeros() > 0 ? T(1) : T(0), y);
 }
 template <typename T>
 void Matrix<T>::spmv_sym(T* x, T* y) const
 {
-  _mat_local->mult(1, x, 0, y);
+  {
+    detail::NvtxRange r("spmv:local block (symmetric)");
+    _mat_local->mult(1, x, 0, y);
+  }
+  detail::NvtxRange r("spmv:remote block");
   _mat_remote->mult(1, x, 1, y);
 }
 template <typename T>
 void Matrix<T>::spmv_sym_overlap(T* x, T* y) const
 {
-  _mat_local->mult(1, x, 0, y);
+  {
+    detail::NvtxRange r("spmv:local block (symmetric)");
+    _mat_local->mult(1, x, 0, y);
+  }
   _col_map->update_finalise(x);
+  detail::NvtxRange r("spmv:remote block");
   _mat_remote->mult(1, x, 1, y);
 }
 //-----------------------------------------------------------------------------

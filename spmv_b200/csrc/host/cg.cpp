@@ -280,6 +280,7 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
       mark(2);
       mark(3);
     }
+    detail::NvtxRange nv("cg:vector step + reductions");
     if (fused_vec) {
       detail::check(b200_cg_fused_step_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, single ? 0 : 1, stream),
                     "cg fused step");

@@ -10,10 +10,30 @@
 #include <string>
 #include <vector>
 
+// NVTX ranges around the phases of the path (pack / exchange / local block / remote block / vector step +
+// reductions), so a timeline shows the same five bars the reference's demo timers print (demos/spmv.cpp:86-102).
+// Header-only nvtx3: a no-op unless a profiler injects itself; compiled out where the header is missing.
+#if defined(__has_include)
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>
+#define SPMV_HAVE_NVTX 1
+#endif
+#endif
+
 namespace spmv
 {
 namespace detail
 {
+struct NvtxRange {
+#ifdef SPMV_HAVE_NVTX
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+#else
+  explicit NvtxRange(const char*) {}
+#endif
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 /// C-ABI status -> exception, the way the reference's constructors throw
 /// std::runtime_error (Matrix.cpp:29, L2GMap.cpp:363).

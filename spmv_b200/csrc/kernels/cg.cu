@@ -324,10 +324,24 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const int stride = gridDim.x * blockDim.x;
   const int tid0 = blockIdx.x * blockDim.x + threadIdx.x;
 
+  // 16-byte accesses when the vectors allow it (they come from cudaMalloc: always, unless a caller offsets them)
+  const bool vec2 = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(Ap) | reinterpret_cast<uintptr_t>(x)
+                      | reinterpret_cast<uintptr_t>(r)) & 15) == 0;
+  const int n2 = vec2 ? n >> 1 : 0; // pairs handled as double2; [2*n2, n) one by one
+  double2* p2 = reinterpret_cast<double2*>(p);
+  const double2* Ap2 = reinterpret_cast<const double2*>(Ap);
+  double2* x2 = reinterpret_cast<double2*>(x);
+  double2* r2 = reinterpret_cast<double2*>(r);
+
   double pAp;
   if (need_dot) { // cg.cpp:63-65
     dd acc = {0.0, 0.0};
-    for (int i = tid0; i < n; i += stride)
+    for (int i = tid0; i < n2; i += stride) {
+      const double2 u = p2[i], w = Ap2[i];
+      dd_add_prod(acc, u.x, w.x);
+      dd_add_prod(acc, u.y, w.y);
+    }
+    for (int i = 2 * n2 + tid0; i < n; i += stride)
       dd_add_prod(acc, p[i], Ap[i]);
     pAp = fused_grid_allreduce(acc, st, peer, gen0 + 1, s_warp, &s_bcast);
   } else if (peer != nullptr) { // the SpMV epilogue left this rank's p.Ap in st[ST_PAP]
@@ -341,20 +355,40 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const double alpha = (rnorm_old * rnorm_old) / pAp; // cg.cpp:66
   const double nalpha = -alpha;
   dd acc = {0.0, 0.0};
-  for (int i = tid0; i < n; i += stride) {
+  for (int i = tid0; i < n2; i += stride) {
+    const double2 pi = p2[i], api = Ap2[i];
+    double2 xi = x2[i], ri = r2[i];
+    xi.x = __dadd_rn(xi.x, __dmul_rn(alpha, pi.x));  // cg.cpp:69
+    xi.y = __dadd_rn(xi.y, __dmul_rn(alpha, pi.y));
+    ri.x = __dadd_rn(ri.x, __dmul_rn(nalpha, api.x)); // cg.cpp:70
+    ri.y = __dadd_rn(ri.y, __dmul_rn(nalpha, api.y));
+    x2[i] = xi;
+    r2[i] = ri;
+    dd_add_prod(acc, ri.x, ri.x);                     // cg.cpp:73
+    dd_add_prod(acc, ri.y, ri.y);
+  }
+  for (int i = 2 * n2 + tid0; i < n; i += stride) {
     const double pi = p[i], api = Ap[i];
-    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, pi));              // cg.cpp:69
-    const double ri = __dadd_rn(r[i], __dmul_rn(nalpha, api)); // cg.cpp:70
+    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, pi));
+    const double ri = __dadd_rn(r[i], __dmul_rn(nalpha, api));
     r[i] = ri;
-    dd_add_prod(acc, ri, ri);                                  // cg.cpp:73
+    dd_add_prod(acc, ri, ri);
   }
   const double rr = fused_grid_allreduce(acc, st, peer, gen0 + 2, s_warp, &s_bcast);
   const double rnorm_new = sqrt(rr);                                      // cg.cpp:76
   const double beta = (rnorm_new * rnorm_new) / (rnorm_old * rnorm_old);  // cg.cpp:77
   const bool converged = (rnorm_new / rnorm0) < rtol;                     // cg.cpp:80
-  if (!converged)
-    for (int i = tid0; i < n; i += stride)
-      p[i] = __dadd_rn(__dmul_rn(beta, p[i]), r[i]);                      // cg.cpp:84-85
+  if (!converged) {
+    for (int i = tid0; i < n2; i += stride) {                             // cg.cpp:84-85
+      double2 pi = p2[i];
+      const double2 ri = r2[i];
+      pi.x = __dadd_rn(__dmul_rn(beta, pi.x), ri.x);
+      pi.y = __dadd_rn(__dmul_rn(beta, pi.y), ri.y);
+      p2[i] = pi;
+    }
+    for (int i = 2 * n2 + tid0; i < n; i += stride)
+      p[i] = __dadd_rn(__dmul_rn(beta, p[i]), r[i]);
+  }
   if (tid0 == 0) { // nobody reads these again in this launch (everybody took its copies above)
     const int iter = (int)st[ST_ITER] + 1;
     st[ST_ITER] = (double)iter;
