@@ -636,6 +636,7 @@ def run_b200(args):
         if size == 1 and not args.no_library_context:
             # what the reference's CUDA backend would run on this GPU: cusparseSpMV + cuBLAS BLAS-1 (library code)
             also["library_context"] = {"cusparse_general_27pt": measure_cusparse(dev, nz),
+                                       "cusparse_powerlaw_3M": measure_cusparse_powerlaw(api, dev),
                                        "cublas_cg_vector_ops": measure_cublas_blas1(dev, NX * NY * nz)}
         # ---- config 1: the reference's own demo loop on create_A(1e6) --------------------------
         also["config1_createA"] = measure_config1(api, ex, dev, rank, size, timer)
@@ -692,6 +693,46 @@ def measure_cusparse(dev, nz, steps=20, warmup=3):
         return {"ms_per_step": ms, "GBps": nbytes / ms / 1e6, "how": "torch.sparse_csr_tensor(int32, fp64).matmul -> cusparseSpMV"}
     except Exception as e:  # opt-in context measurement: never fail the bench over it
         return {"error": str(e)[:200]}
+
+
+def measure_cusparse_powerlaw(api, dev, rows=3_000_000, steps=20):
+    """cusparseSpMV (torch.sparse CSR) and this repo's kernel on the same 3 M-row power-law matrix (config 5's row
+    shape): the library number the irregular-row walk is up against.  Context only."""
+    try:
+        import numpy as np
+        import torch
+        from spmv_b200 import kernels as K
+        from spmv_b200 import synth
+        rp, col, val = api.powerlaw_rows(rows, 0, rows)
+        rp_d = torch.from_numpy(rp.astype(np.int32)).to(dev)
+        ci_d = torch.from_numpy(col.astype(np.int32)).to(dev)
+        v_d = torch.from_numpy(val).to(dev)
+        x = torch.from_numpy(synth.bump_vector(rows, 0, rows)).to(dev)
+        y = torch.empty(rows, dtype=torch.float64, device=dev)
+        A = torch.sparse_csr_tensor(rp_d, ci_d, v_d, size=(rows, rows))
+        plan = K.CsrPlan(rows, rows, rp_d, False, nnz=int(rp[-1]))
+
+        def timed(fn):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / steps
+
+        ms_lib = timed(lambda: A.matmul(x))
+        ms_own = timed(lambda: K.spmv(plan, rp_d, ci_d, v_d, x, y))
+        err = float((A.matmul(x) - y).norm() / y.norm())
+        nbytes = bytes_general(int(rp[-1]), 0, rows, rows, False)
+        plan.close()
+        return {"rows": rows, "nnz": int(rp[-1]), "cusparse_ms": ms_lib, "cusparse_GBps": nbytes / ms_lib / 1e6,
+                "this_repo_ms": ms_own, "this_repo_GBps": nbytes / ms_own / 1e6, "rel_diff": err}
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"[:200]}
 
 
 def measure_cublas_blas1(dev, m, iters=20):

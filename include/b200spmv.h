@@ -83,13 +83,26 @@ B200_API int b200_csr_plan_info(void* plan, int32_t* num_tiles, int32_t* max_row
  * ring, walk chosen from the row-length histogram (default); 1 = one tile per CTA staged
  * with plain loads; 2..5 = variant 0 with the walk forced: 2 one thread per row in chunks
  * of 16 entries, 3 two-phase stream walk, 4 chunks of 8, 5 chunks of 4, 6 warp-private
- * stream walk (general storage; each consumer warp owns a plan-time segment of the tile, no
- * CTA barrier; symmetric plans fall back to 3).  consumer_warps is 8 or 16.  Re-partitions
+ * software-pipelined stream walk (general storage; each consumer warp owns a plan-time segment of
+ * the tile, no CTA barrier), 7 the same with L1::no_allocate gathers, 8 split stream walk (half of
+ * the consumer warps make the products of tile i+1 while the other half sums the rows of tile i;
+ * the default for irregular rows in general storage); symmetric plans fall back from 6-8 to 3.
+ * consumer_warps is 8 or 16.  Re-partitions
  * the tiles (needs the same d_rowptr the plan was created with).
  * Defaults also read B200_SPMV_{VARIANT,TILE_BYTES,STAGES,CWARPS,CTAS} from the
  * environment at plan creation. */
 B200_API int b200_csr_plan_tune(void* plan, const int32_t* d_rowptr, int variant, int tile_bytes,
                        int stages, int consumer_warps, int ctas_per_sm, void* stream);
+
+/* Memory contract of the SpMV entries below.  The pipeline moves the matrix with 16-byte bulk copies, each
+ * slice starting at the 16-byte aligned element at or below its first element and rounded up to a 16-byte
+ * multiple: up to 12 bytes BEHIND the last element of d_val / d_colind / d_rowptr (and, symmetric storage,
+ * d_diag and d_x) can be read and are never used.  The read stays inside the last element's 16-byte unit, so
+ * any allocation whose size is rounded to 16 bytes (cudaMalloc rounds to 256) covers it; a caller that
+ * sub-allocates exact-size arrays at the very end of a mapping must pad them to a 16-byte multiple (and
+ * compute-sanitizer memcheck reports the read otherwise).  Base pointers that are not 16-byte aligned are
+ * accepted and routed to the plain-load kernel.  With an overlapping schedule the over-read of x may touch the
+ * first ghost entry while the exchange writes it: harmless, the value is not used. */
 
 /* ---- general CSR SpMV: CSRSpMV<T>::run, general branch
  *      (csr_kernels.cpp:41-51; replaces cusparseSpMV at

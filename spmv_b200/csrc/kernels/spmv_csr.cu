@@ -760,6 +760,8 @@ __device__ __forceinline__ dd split_sums(const SpmvArgs<T>& a, unsigned char* sm
       const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
       const unsigned char* stage = smem + (size_t)s * sb;
       const T* sv = reinterpret_cast<const T*>(stage) + (lo - L.lo_v);
+      const int par = (lo - L.lo_v) & 1; // sv[j] is 16-byte aligned iff j + par is even
+      (void)par;
       const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r);
       for (int k0 = warp * 32; k0 < ns; k0 += NT) {
         const int k = k0 + lane;
@@ -771,14 +773,36 @@ __device__ __forceinline__ dd split_sums(const SpmvArgs<T>& a, unsigned char* sm
         const bool is_long = re - rs > SHORT_ROW;
         if (k < ns && !is_long) {
           T sum = T(0);
-          for (int b = rs; b < re; b += C) {
-            T pv[C];
+          if constexpr (sizeof(T) == 8) {
+            // 16-byte loads: the shared-memory data pipe is what this kernel runs out of (80 % busy, profiles/
+            // r02_powerlaw_split_ncu_summary.txt) and a quarter-warp of random 16-byte reads costs fewer
+            // wavefronts per value than a half-warp of 8-byte ones.  One scalar load brings the row to alignment.
+            int b = rs;
+            if (((b + par) & 1) && b < re) {
+              sum = add_rn(sum, sv[b]);
+              ++b;
+            }
+            for (; b < re; b += C) {
+              double2 q[C / 2];
 #pragma unroll
-            for (int u = 0; u < C; ++u)
-              pv[u] = b + u < re ? sv[b + u] : T(0);
+              for (int u = 0; u < C / 2; ++u)
+                q[u] = b + 2 * u < re ? *reinterpret_cast<const double2*>(sv + b + 2 * u) : make_double2(0.0, 0.0);
 #pragma unroll
-            for (int u = 0; u < C; ++u)
-              sum = add_rn(sum, pv[u]);
+              for (int u = 0; u < C / 2; ++u) {
+                sum = add_rn(sum, q[u].x);
+                sum = add_rn(sum, b + 2 * u + 1 < re ? q[u].y : 0.0); // the pair's second half may be the next row's
+              }
+            }
+          } else {
+            for (int b = rs; b < re; b += C) {
+              T pv[C];
+#pragma unroll
+              for (int u = 0; u < C; ++u)
+                pv[u] = b + u < re ? sv[b + u] : T(0);
+#pragma unroll
+              for (int u = 0; u < C; ++u)
+                sum = add_rn(sum, pv[u]);
+            }
           }
           const T out = store_row<T, false>(a, r0 + k, sum);
           if (DOT)
