@@ -4,21 +4,17 @@ mkdir -p gpurun_out
 nvidia-smi topo -m > gpurun_out/r02_topo_n8.txt 2>&1
 nproc > gpurun_out/r02_nproc.txt; free -g >> gpurun_out/r02_nproc.txt
 tr() { timeout $1 python -m torch.distributed.run --nnodes=1 --nproc-per-node $2 --master-addr 127.0.0.1 --master-port $3 "${@:4}"; }
-timeout 600 python -m pytest tests/test_dist.py -x -q -m gpu > gpurun_out/r02_pytest_dist_n8.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_dist_n8.log
-tail -4 gpurun_out/r02_pytest_dist_n8.log | cut -c1-300
-for n in 8 4 2; do
-  tr 200 $n 295$n profiles/tools/pcie_probe_n.py > gpurun_out/r02_pcie_n${n}_unbound.json 2> gpurun_out/r02_pcie.err
-  tr 200 $n 296$n profiles/tools/pcie_probe_n.py --bind > gpurun_out/r02_pcie_n${n}_bound.json 2>> gpurun_out/r02_pcie.err
-done
+tr 200 8 29508 profiles/tools/pcie_probe_n.py > gpurun_out/r02_pcie_n8_unbound.json 2> gpurun_out/r02_pcie.err
+tr 200 8 29608 profiles/tools/pcie_probe_n.py --bind > gpurun_out/r02_pcie_n8_bound.json 2>> gpurun_out/r02_pcie.err
+tr 200 4 29604 profiles/tools/pcie_probe_n.py --bind > gpurun_out/r02_pcie_n4_bound.json 2>> gpurun_out/r02_pcie.err
 cat gpurun_out/r02_pcie_n8_unbound.json gpurun_out/r02_pcie_n8_bound.json | cut -c1-900
 run() { tr 900 $1 $2 bench.py --gpus $1 --steps 20 --warmup 3 $3 > gpurun_out/$4.json 2> gpurun_out/$4.err; echo "$4 rc=$?"; tail -2 gpurun_out/$4.err | cut -c1-300; }
 run 8 29701 "" r02_bench_n8_a
 run 8 29702 "--strong --config5-rows 0" r02_bench_n8_strong_a
 run 4 29703 "--strong --config5-rows 0" r02_bench_n4_strong_a
-run 4 29704 "--config5-rows 0" r02_bench_n4_a
 python - <<'PY'
 import json
-for f in ("r02_bench_n8_a","r02_bench_n8_strong_a","r02_bench_n4_strong_a","r02_bench_n4_a"):
+for f in ("r02_bench_n8_a","r02_bench_n8_strong_a","r02_bench_n4_strong_a"):
     try:
         d=json.load(open(f"gpurun_out/{f}.json"))
     except Exception as e:
@@ -31,3 +27,5 @@ for f in ("r02_bench_n8_a","r02_bench_n8_strong_a","r02_bench_n4_strong_a","r02_
     if "powerlaw_petsc" in a: print(" pl", a["powerlaw_petsc"]["ms_per_step"], a["powerlaw_petsc"]["local_kernel_frac_of_hbm_peak"], a["powerlaw_petsc"]["parity"]["max_rel_err"])
     if "config1_createA" in a: print(" c1", a["config1_createA"]["us_per_step"], a["config1_createA"]["parity"])
 PY
+timeout 400 python -m pytest tests/test_dist.py -x -q -m gpu > gpurun_out/r02_pytest_dist_n8.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_dist_n8.log
+tail -12 gpurun_out/r02_pytest_dist_n8.log | cut -c1-300
