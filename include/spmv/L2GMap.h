@@ -134,6 +134,7 @@ private:
   bool _halo_kernel = false;
   void* _halo_desc = nullptr;
   mutable void* _pending_tail = nullptr;
+  mutable bool _pending_on_comm = false; // ... and its push went to the side stream
   bool _peer_ok = false;
   char* _stage = nullptr;            // my staging buffer (cudaMalloc, IPC-exported)
   size_t _slot_bytes = 0;

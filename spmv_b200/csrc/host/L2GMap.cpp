@@ -388,10 +388,13 @@ void L2GMap::finish_kernel_halo() const
   if (!_pending_tail)
     return;
   const B200Executor* gpu = as_b200(_exec);
+  if (_pending_on_comm) // the push ran on the side stream: its epoch must be in place before the wait kernel reads it
+    detail::check(b200_stream_wait_event(gpu->get_cuda_stream(), gpu->arrived_event()), "stream wait");
   detail::check(halo_wait(_halo_desc, static_cast<std::int64_t>(_ghosts.size()), static_cast<T*>(_pending_tail),
                           gpu->get_cuda_stream()),
                 "halo wait + unpack");
   _pending_tail = nullptr;
+  _pending_on_comm = false;
 }
 //-----------------------------------------------------------------------------
 template <typename T>
@@ -403,7 +406,19 @@ void L2GMap::exchange_forward(T* vec_data, bool overlap) const
       return;
     detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
     finish_kernel_halo<T>(); // an exchange the caller never finalised: its slot must be drained before the next push
-    detail::check(halo_push(_halo_desc, _num_indices, _indexbuf, vec_data, gpu->get_cuda_stream()), "halo push");
+    void* stream = gpu->get_cuda_stream();
+    if (overlap) {
+      // Overlapping models: the push goes to the side stream, behind an event that says "x is ready", so that its
+      // NVLink stores and system-scope fence run under whatever the caller enqueues next on the compute stream
+      // (Matrix::mult: the local block).  Fork and join are events, so a stream capture follows both streams.
+      detail::check(b200_event_record(gpu->packed_event(), stream), "event record");
+      detail::check(b200_stream_wait_event(gpu->comm_stream(), gpu->packed_event()), "stream wait");
+      stream = gpu->comm_stream();
+    }
+    detail::check(halo_push(_halo_desc, _num_indices, _indexbuf, vec_data, stream), "halo push");
+    if (overlap)
+      detail::check(b200_event_record(gpu->arrived_event(), stream), "event record");
+    _pending_on_comm = overlap;
     _pending_tail = vec_data + (_ranges[_mpi_rank + 1] - _ranges[_mpi_rank]);
     if (!overlap)
       finish_kernel_halo<T>();

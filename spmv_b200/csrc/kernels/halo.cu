@@ -119,10 +119,11 @@ __global__ void __launch_bounds__(256) halo_push_kernel(HaloDesc* d, int n, cons
     T* dst = reinterpret_cast<T*>(d->peer_slot[slot][i]) + d->land[i] + (k - d->send_off[i]);
     *dst = __ldg(x + __ldg(idx + k));
   }
-  __threadfence_system(); // my stores are ordered before the ticket for every observer
   __syncthreads();
-  if (threadIdx.x == 0)
+  if (threadIdx.x == 0) {
+    __threadfence_system(); // cumulative: the CTA's stores (ordered before me by the barrier) precede the ticket
     s_last = atomicAdd(&d->ticket, 1u) == gridDim.x - 1;
+  }
   __syncthreads();
   if (s_last) {
     __threadfence_system();
