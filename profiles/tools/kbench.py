@@ -59,10 +59,6 @@ def powerlaw(a, dev):
         if variant == 3:
             shapes += [(16384, 2, 16, 2), (16384, 2, 16, 3), (24576, 2, 16, 3), (16384, 3, 16, 3), (24576, 3, 16, 2),
                        (24576, 3, 8, 4), (12288, 2, 16, 3), (12288, 3, 16, 3), (49152, 3, 16, 1), (20480, 2, 16, 3)]
-        if variant == 9:  # chunk walk: a warp's share should be a multiple of 256 entries
-            shapes = [(24576, 2, 8, 3), (24576, 3, 8, 2), (24576, 2, 8, 2), (24576, 3, 8, 3), (16384, 3, 8, 3), (16384, 2, 8, 4),
-                      (32768, 2, 8, 2), (49152, 2, 16, 1), (49152, 2, 16, 2), (49152, 3, 16, 1), (32768, 2, 16, 2),
-                      (24576, 2, 16, 2), (12288, 2, 8, 4), (12288, 3, 8, 4), (49152, 2, 8, 2), (65536, 2, 16, 1)]
         if variant == 8:  # split walk: A warps products, B warps sums
             shapes = [(24576, 2, 16, 2), (24576, 3, 16, 2), (16384, 3, 16, 2), (16384, 4, 16, 2), (12288, 4, 16, 2),
                       (20480, 3, 16, 2), (32768, 2, 16, 2), (49152, 3, 16, 1), (32768, 4, 16, 1),

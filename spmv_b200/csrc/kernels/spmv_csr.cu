@@ -56,10 +56,7 @@ constexpr int WALK_ROW8S = 4, WALK_ROW4S = 5;
 constexpr int WALK_SEG = 6;
 // the same with L1::no_allocate x gathers
 constexpr int WALK_SEGNA = 7;
-// chunk walk (general storage): products stay in registers, rows are summed by an order-preserving carry
-// between lanes; warp segments as for WALK_SEG
-constexpr int WALK_CHUNK = 9;
-__host__ __device__ constexpr bool walk_is_seg(int w) { return w == WALK_SEG || w == WALK_SEGNA || w == WALK_CHUNK; }
+__host__ __device__ constexpr bool walk_is_seg(int w) { return w == WALK_SEG || w == WALK_SEGNA; }
 // split stream walk (general storage): half of the consumer warps make the products of tile i+1
 // while the other half sums the rows of tile i; hand-over through mbarriers only
 constexpr int WALK_SPLIT = 8;
@@ -686,199 +683,6 @@ __device__ __forceinline__ dd seg_consumer(const SpmvArgs<T>& a, unsigned char* 
 }
 
 // ---------------------------------------------------------------------------
-// Chunk walk (WALK_CHUNK; general storage, irregular row lengths): no shared-memory round trip of the
-// products.  The stream and split walks spend most of the L1TEX data pipe -- the unit this matrix class is
-// bound by (profiles/r02_powerlaw_walks.md) -- on writing 8-byte products to shared memory and reading them
-// back one lane per row (bank conflicts: 2.5 values per wavefront).  Here a warp takes its segment of the
-// tile (rows that start in its share of the entries, as for WALK_SEG) in chunks of 256 consecutive entries,
-// lane l owning entries 8l .. 8l+7:
-//   * column indices and values come in with conflict-free 16-byte loads, the eight x gathers go out together,
-//     the products stay in registers;
-//   * the row that holds a lane's first entry is found by all lanes together: 32 row ends per coalesced load,
-//     a 6-probe binary search over them with shuffles;
-//   * each lane walks its eight entries, finishing rows as their ends pass (a finished row is stored at once);
-//   * a row that crosses lanes is continued IN ORDER: the lane holding its next entries adds them, left to
-//     right, onto the value carried over from the lane before (shuffle), so every row sum is the reference's
-//     left-to-right sum (csr_kernels.cpp:45-47) whatever its length -- bit-identical, long rows included.  The
-//     carry rounds needed are 1 + the longest run of lanes lying wholly inside one row (1-2 for short rows).
-// ---------------------------------------------------------------------------
-template <typename T, bool DOT, int CW>
-__device__ __forceinline__ dd chunk_consumer(const SpmvArgs<T>& a, unsigned char* smem, StageMeta* meta, uint64_t* full,
-                                             uint64_t* empty, int my_tiles, int warp, int lane, double* s_warp)
-{
-  constexpr unsigned FULL = 0xffffffffu;
-  constexpr int E = 8;      // entries per lane and chunk
-  constexpr int CH = 32 * E;
-  constexpr int VU = 16 / (int)sizeof(T); // values per 16-byte unit
-  constexpr int BIG = 0x7fffffff;
-  const int stages = a.stages, sb = a.stage_bytes;
-  dd dot = {0.0, 0.0};
-  auto finish = [&](int row, T sum) { // y[row] is complete
-    const T out = store_row<T, false>(a, row, sum);
-    if (DOT)
-      dd_add_prod(dot, (double)__ldg(a.x + row), (double)out);
-  };
-  for (int it = 0, s = 0, use = 0; it < my_tiles; ++it) {
-    mbar_wait(full + s, use & 1);
-    const StageMeta* m = meta + s;
-    const int ns = m->nstaged, nrows = m->nrows, r0 = m->r0;
-    if (ns > 0) {
-      const int lo = m->lo, hi = m->hi;
-      const TileLayout<T, LAY_PLAIN> L(r0, ns, lo, hi);
-      const unsigned char* stage = smem + (size_t)s * sb;
-      const T* sv = reinterpret_cast<const T*>(stage) + (lo - L.lo_v);                        // sv[j - lo]
-      const int* sc = reinterpret_cast<const int*>(stage + L.off_c()) + (lo - L.lo_c);
-      const int* sr = reinterpret_cast<const int*>(stage + L.off_r()) + (r0 - L.lo_r);        // sr[k], k <= ns
-      const int* wr = reinterpret_cast<const int*>(stage + L.off_d());
-      const int ka = min(wr[warp], ns), kb = min(wr[warp + 1], ns);
-      if (ka < kb) {
-        const int ea = sr[ka] - lo, eb = sr[kb] - lo;
-        if (a.flags & 4) // the plan saw empty rows: they have no entry to carry them
-          for (int k = ka + lane; k < kb; k += 32)
-            if (sr[k + 1] == sr[k])
-              finish(r0 + k, T(0));
-        const int A8 = lo & 7; // (j + A8) % 8 == 0  <=>  entry j starts a 16-byte unit of both staged arrays
-        int rowbase = ka;      // no row before it holds an entry of the chunk
-        T carry = T(0);        // running sum of the row that crosses into the chunk
-        for (int cs = ea - ((ea + A8) & 7); cs < eb; cs += CH) {
-          const int jb = cs + E * lane;
-          const int u0 = max(ea - jb, 0), u1 = min(eb - jb, E); // my valid entries are u in [u0, u1)
-          const bool any = u0 < u1;
-          // ---- 16-byte loads of the lane's column indices and values (units that hold a valid entry only) ----
-          int c[E];
-          T p[E];
-#pragma unroll
-          for (int q = 0; q < E / 4; ++q) {
-            int4 w = make_int4(0, 0, 0, 0);
-            if (u0 < 4 * q + 4 && u1 > 4 * q)
-              w = *reinterpret_cast<const int4*>(sc + jb + 4 * q);
-            c[4 * q] = w.x, c[4 * q + 1] = w.y, c[4 * q + 2] = w.z, c[4 * q + 3] = w.w;
-          }
-#pragma unroll
-          for (int q = 0; q < E / VU; ++q) {
-            if (u0 < VU * q + VU && u1 > VU * q) {
-              const uint4 w = *reinterpret_cast<const uint4*>(sv + jb + VU * q);
-              if constexpr (sizeof(T) == 8) {
-                p[2 * q] = __hiloint2double((int)w.y, (int)w.x);
-                p[2 * q + 1] = __hiloint2double((int)w.w, (int)w.z);
-              } else {
-                p[4 * q] = __uint_as_float(w.x), p[4 * q + 1] = __uint_as_float(w.y);
-                p[4 * q + 2] = __uint_as_float(w.z), p[4 * q + 3] = __uint_as_float(w.w);
-              }
-            } else {
-#pragma unroll
-              for (int t = 0; t < VU; ++t)
-                p[VU * q + t] = T(0);
-            }
-          }
-          T xv[E];
-#pragma unroll
-          for (int u = 0; u < E; ++u)
-            xv[u] = (u >= u0 && u < u1) ? __ldg(a.x + c[u]) : T(0);
-          // ---- the row of my first valid entry: count the row ends at or before it ----
-          const int jf = jb + u0;
-          int cnt = 0;
-          {
-            bool searching = any;
-            int base = rowbase + 1;
-            do {
-              const int idx = base + lane;
-              const int e_i = idx <= kb ? sr[idx] - lo : BIG; // ascending; BIG pads the batch
-              int pos = 0;
-#pragma unroll
-              for (int stp = 16; stp >= 1; stp >>= 1) {
-                const int em = __shfl_sync(FULL, e_i, pos + stp - 1);
-                if (em <= jf)
-                  pos += stp;
-              }
-              {
-                const int em = __shfl_sync(FULL, e_i, min(pos, 31));
-                if (pos == 31 && em <= jf)
-                  pos = 32;
-              }
-              if (searching) {
-                cnt += pos;
-                searching = pos == 32;
-              }
-              base += 32;
-            } while (__any_sync(FULL, searching));
-          }
-          int r = any ? rowbase + cnt : kb;          // my current row (tile-relative)
-          int end = any ? sr[r + 1] - lo : BIG;      // ... and where it ends
-          const bool open = any && (sr[r] - lo < jf); // it began before my first entry: its value so far is carried in
-#pragma unroll
-          for (int u = 0; u < E; ++u)
-            p[u] = mul_rn(p[u], xv[u]);
-          // ---- walk my entries: rows that end inside them are finished here ----
-          T sum = T(0);
-          bool head = open; // still inside the carried-in row
-          int nh = 0, head_row = r;
-          bool head_done_here = false; // the carried-in row ends inside my entries
-#pragma unroll
-          for (int u = 0; u <= E; ++u) {
-            const int j = jb + u;
-            if (any && u >= u0 && u <= u1 && j == end) { // row r ended just before entry j
-              if (head) {
-                head = false;
-                head_done_here = true;
-                nh = u - u0;
-                head_row = r;
-              } else {
-                finish(r0 + r, sum);
-              }
-              ++r;
-              while (r < kb && sr[r + 1] - lo == j)
-                ++r; // empty rows
-              end = r < kb ? sr[r + 1] - lo : BIG;
-              sum = T(0);
-            }
-            if (u < E && u >= u0 && u < u1)
-              sum = add_rn(sum, p[u]);
-          }
-          // ---- carried-in rows, in order.  tail = value my successor continues from ----
-          bool need = open;               // my head still waits for the value carried in
-          bool ready = !(open && head);   // my tail does not depend on it (or I hold no entries)
-          T tail = sum;
-          do {
-            T cin = __shfl_up_sync(FULL, tail, 1);
-            int cready = __shfl_up_sync(FULL, (int)ready, 1);
-            if (lane == 0) {
-              cin = carry;
-              cready = 1;
-            }
-            if (need && cready) {
-              T hs = cin;
-              const int hn = head_done_here ? nh : u1 - u0;
-#pragma unroll
-              for (int u = 0; u < E; ++u)
-                if (u >= u0 && u < u0 + hn)
-                  hs = add_rn(hs, p[u]);
-              if (head_done_here)
-                finish(r0 + head_row, hs);
-              else
-                tail = hs; // all my entries lie inside the carried-in row
-              need = false;
-              ready = true;
-            }
-          } while (__any_sync(FULL, need));
-          carry = __shfl_sync(FULL, tail, 31);
-          rowbase = min(__shfl_sync(FULL, r, 31), kb - 1);
-        }
-      }
-    }
-    if (ns < nrows)
-      dot = dd_merge(dot, walk_direct_cta<T, false, DOT>(a, r0 + ns, nrows - ns, threadIdx.x, CW * 32, warp, CW, lane, 1,
-                                                         s_warp));
-    __syncwarp();
-    if (lane == 0)
-      mbar_arrive(empty + s);
-    s = s + 1 == stages ? 0 : s + 1;
-    use += s == 0;
-  }
-  return dot;
-}
-
-// ---------------------------------------------------------------------------
 // Split stream walk (WALK_SPLIT; general storage, irregular row lengths).  The stream walk's two
 // phases run on DIFFERENT warps, one tile apart:
 //   A warps (first half of the consumers): products.  Entry-parallel over the whole tile, every lane
@@ -1318,8 +1122,6 @@ __global__ void __launch_bounds__((CW + 1) * 32, pipe_min_ctas(SYM, WALK, CW)) s
     }
     // (scratch of the direct walk behind the 2 * CW doubles the dot reduction uses: the A warps may be in it already)
     dot = split_sums<T, DOT, NB>(a, smem, meta, prod, empty, my_tiles, warp - NA, lane, s_warp + 32);
-  } else if constexpr (SEGW && WALK == WALK_CHUNK) {
-    dot = chunk_consumer<T, DOT, CW>(a, smem, meta, full, empty, my_tiles, warp, lane, s_warp);
   } else if constexpr (SEGW) {
     dot = seg_consumer<T, DOT, CW, WALK == WALK_SEGNA>(a, smem, meta, full, empty, my_tiles, warp, lane, s_warp);
   } else
@@ -1733,9 +1535,6 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
   case WALK_SPLIT:
     *tile_bytes = 16 * 1024, *stages = 3, *cw = 16, *ctas = 2;
     break;
-  case WALK_CHUNK:
-    *tile_bytes = 24 * 1024, *stages = 2, *cw = 8, *ctas = 3;
-    break;
   default:
     *tile_bytes = 48 * 1024, *cw = 8, *ctas = 2;
   }
@@ -1744,12 +1543,12 @@ static void plan_default_shape(const Plan* p, int* tile_bytes, int* stages, int*
 // b200_csr_plan_tune's variant -> forced walk (-1: chosen from the histogram)
 static int walk_of_variant(int variant)
 {
-  return variant == 9 ? WALK_CHUNK : variant == 8 ? WALK_SPLIT : variant == 7 ? WALK_SEGNA : variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
+  return variant == 8 ? WALK_SPLIT : variant == 7 ? WALK_SEGNA : variant == 6 ? WALK_SEG : (variant >= 2 && variant <= 5 ? variant - 2 : -1);
 }
 
 static int plan_apply_tuning(Plan* p, int variant, int tile_bytes, int stages, int cw, int ctas)
 {
-  B200_REQUIRE(variant >= 0 && variant <= 9, "variant must be 0..9");
+  B200_REQUIRE(variant >= 0 && variant <= 8, "variant must be 0..8");
   // 0: pipeline, walk chosen from the histogram; 1: one tile per CTA (row walk);
   // 2..5: pipeline with the walk forced to WALK_ROW16 / WALK_STREAM / WALK_ROW8 / WALK_ROW4;
   // 6: WALK_SEG (general storage; symmetric plans fall back to WALK_STREAM); 7: WALK_SEGNA; 8: WALK_SPLIT
@@ -1842,11 +1641,6 @@ static int launch_pipe_walk(const Plan& p, const SpmvArgs<T>& a, cudaStream_t st
       return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
     else
       return launch_pipe_cw<T, SYM, DOT, false, WALK_SPLIT>(p, a, st);
-  case WALK_CHUNK:
-    if constexpr (SYM)
-      return launch_pipe_cw<T, SYM, DOT, LONG, WALK_STREAM>(p, a, st);
-    else
-      return launch_pipe_cw<T, SYM, DOT, false, WALK_CHUNK>(p, a, st);
   case WALK_ROW8:
     if (p.max_row_len <= 8)
       return launch_pipe_cw<T, SYM, DOT, false, WALK_ROW8S>(p, a, st);
@@ -1968,7 +1762,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   {
     static const int seg_ef = env_int("B200_SPMV_SEG_EVICT_FIRST", 0);
     static const int contig = env_int("B200_SPMV_TILE_CONTIG", 0);
-    a.flags = (seg_ef ? 1 : 0) | (contig ? 2 : 0) | (p.hist[0] > 0 ? 4 : 0);
+    a.flags = (seg_ef ? 1 : 0) | (contig ? 2 : 0);
   }
   a.tile0 = ranged ? tile_begin : 0;
   a.num_tiles = ranged ? tile_end : p.num_tiles;

@@ -41,12 +41,6 @@ SEG_VARIANTS = [
     dict(variant=8, tile_bytes=16384, stages=3, consumer_warps=16, ctas_per_sm=2),
     dict(variant=8, tile_bytes=24576, stages=2, consumer_warps=8, ctas_per_sm=3),
     dict(variant=8, tile_bytes=2048, stages=4, consumer_warps=16, ctas_per_sm=2),
-    # 9 = chunk walk: products in registers, rows summed by an order-preserving carry between lanes
-    dict(variant=9, tile_bytes=24576, stages=2, consumer_warps=8, ctas_per_sm=3),
-    dict(variant=9, tile_bytes=16384, stages=3, consumer_warps=16, ctas_per_sm=2),
-    dict(variant=9, tile_bytes=2048, stages=3, consumer_warps=8, ctas_per_sm=2),
-    dict(variant=9, tile_bytes=1024, stages=5, consumer_warps=16, ctas_per_sm=2),
-    dict(variant=9, tile_bytes=65536, stages=2, consumer_warps=8, ctas_per_sm=1),
 ]
 
 
@@ -184,29 +178,6 @@ def test_tall_block_more_rows_than_columns(cuda, tune):
     short = lens <= 32
     if tune is None or tune["variant"] != 1:
         assert np.array_equal(y[short], want[short])  # one thread, j-ascending: the reference's roundings
-
-
-@pytest.mark.parametrize("tune", [t for t in SEG_VARIANTS if t["variant"] == 9])
-@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (-2.0, 0.25)])
-def test_chunk_walk_is_the_reference_sum_for_every_row(cuda, tune, alpha, beta):
-    """The chunk walk continues a row across lanes and chunks in entry order, so EVERY staged row -- 1, 8, 9, 33,
-    300, 2500 entries, rows of one entry in runs of hundreds, empty rows in runs -- is the reference's left-to-right
-    sum (csr_kernels.cpp:45-47) bit for bit; only a row too long for a stage takes the tree-summing direct walk."""
-    rng = np.random.default_rng(31)
-    ncols = 30000
-    lens = np.concatenate([np.ones(700, np.int64), np.zeros(70, np.int64), [8, 8, 8, 9, 7, 16, 17, 255, 256, 257, 33, 0, 0, 1],
-                           rng.integers(0, 3, 500), rng.integers(1, 40, 600), [300, 0, 513, 1, 0],
-                           np.minimum((4.0 / np.sqrt(1.0 - rng.random(3000))).astype(np.int64), 2500), [0, 0]])
-    rp = np.zeros(len(lens) + 1, dtype=np.int64)
-    np.cumsum(lens, out=rp[1:])
-    col = np.concatenate([np.sort(rng.choice(ncols, size=int(l), replace=False)) for l in lens]).astype(np.int64)
-    val = rng.standard_normal(rp[-1])
-    x, y0 = rng.standard_normal(ncols), rng.standard_normal(len(lens))
-    y, _ = run_general(cuda, rp, col, val, x, ncols, alpha, beta, y0.copy(), tune=tune)
-    want = OK.spmv(rp, col, val, x, alpha, beta, y0)
-    staged = lens * 12 + 8 <= tune["tile_bytes"]  # rows that surely fit a stage
-    assert rel_l2(y, want) < TOL
-    assert np.array_equal(y[staged], want[staged])
 
 
 @pytest.mark.parametrize("long_rows", [False, True])
