@@ -247,8 +247,30 @@ def measure_spmv(op, timer, steps, warmup, peak, with_e2e):
         err = float((torch.from_numpy(yh_np) - op.y.cpu()).abs().max() / op.y.abs().max().cpu())
         if not err <= 1e-13:
             raise RuntimeError(f"mult_host disagrees with update+mult: rel max err {err}")
+        # the link's floor for this step: the same bytes up and down at once on two streams, every rank at the same
+        # time, no kernel at all (what profiles/tools/pcie_probe_n.py measures stand-alone)
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        xd, yd = op.x[:M], op.y
+
+        def floor_step(_i):
+            cur = torch.cuda.current_stream()
+            s1.wait_stream(cur)
+            s2.wait_stream(cur)
+            with torch.cuda.stream(s1):
+                xd.copy_(xh, non_blocking=True)
+            with torch.cuda.stream(s2):
+                yh.copy_(yd, non_blocking=True)
+            cur.wait_stream(s1)
+            cur.wait_stream(s2)
+
+        for i in range(2):
+            floor_step(i)
+        ms_floor = timer.run(floor_step, 5) / 5
         out["e2e"] = {"value": op.algorithmic_bytes() * op.size / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s",
-                      "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M}
+                      "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * M, "d2h_bytes_per_step": 8 * M,
+                      "pcie_floor_ms": ms_floor, "over_floor": ms_e2e / ms_floor,
+                      "floor_how": "H2D of x and D2H of y (the step's bytes) concurrently on two streams, all ranks at once, "
+                                   "no kernel; max over ranks"}
     return out
 
 

@@ -108,6 +108,8 @@ def main():
               (False, api.COLLECTIVE_NONBLOCKING), (True, api.COLLECTIVE_BLOCKING), (True, api.P2P_NONBLOCKING)]
     for kind, n in problems:
         N, rows = cases.make_problem(kind, n)
+        if N < 2 * size:
+            continue  # (the 5-row fixture at 4+ ranks: ranks without rows are not a case the reference runs either)
         x_fn = lambda r0, r1: synth.bump_vector(N, r0, r1) + 0.1  # noqa: E731
         for sym, cm in combos:
             if sym and kind == "powerlaw":
@@ -160,10 +162,10 @@ def main():
                     xr = ref["cg_x"]
                     err = np.linalg.norm(xs.cpu().numpy() - xr) / max(np.linalg.norm(xr), 1e-300)
                     check(err < 1e-7, tag + f": cg x rel err {err}")
-                    if not sym and kind in ("lap27", "lap7") and size <= 2:
-                        # bit-identical SpMV + order-independent (Dot2) dot products on both sides:
-                        # the GPU follows the reference's trajectory exactly (two partial sums add
-                        # commutatively, so this holds at 2 ranks as well)
+                    if not sym and kind in ("lap27", "lap7"):
+                        # bit-identical SpMV + order-independent (Dot2) dot products on both sides, and the sum over
+                        # the ranks runs in rank order on both sides (peer allreduce / fused step here, the thread-rank
+                        # shim's MPI_Allreduce there): the GPU follows the reference's trajectory exactly at any rank count
                         check(it == ref["cg_it"] and np.array_equal(xs.cpu().numpy(), xr),
                               tag + f": cg not bit-identical to the reference (its {it} vs {ref['cg_it']}, err {err})")
             A.close()
@@ -216,6 +218,8 @@ def main():
         from oracle import plan as OP
         for kind, n in (("fixture", None), ("lap7", (7, 6, 8)), ("powerlaw", 4000)):
             N, rows = cases.make_problem(kind, n)
+            if N < 2 * size:
+                continue
             inps = [cases.local_inputs(rows, N, r, size) for r in range(size)]
             plans = OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps])
             for halo in ("peer", "nccl"):
@@ -259,6 +263,8 @@ def main():
                                  ("lap7", (7, 6, 8), True, api.P2P_NONBLOCKING), ("lap27", (6, 5, 8), False, api.P2P_NONBLOCKING),
                                  ("lap27", (6, 5, 8), False, api.COLLECTIVE_BLOCKING)):
             N, rows = cases.make_problem(kind, n)
+            if N < 2 * size:
+                continue
             inp = cases.local_inputs(rows, N, rank, size)
             A = api.MatrixF32.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"].astype(np.float32),
                                             inp["nrows_local"], inp["ncols_local"], [], inp["col_ghosts"], sym, cm)
