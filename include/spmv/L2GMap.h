@@ -88,7 +88,18 @@ public:
   /// "nccl" (grouped send/recv) or "none" (one rank): how update() moves the halo
   const char* halo_mode() const
   {
-    return _ranges.size() <= 2 ? "none" : _halo_kernel ? "kernel" : _peer_ok ? "copy" : "nccl";
+    return _ranges.size() <= 2 ? "none" : (_halo_kernel && _use_kernel) ? "kernel" : _peer_ok ? "copy" : "nccl";
+  }
+  /// Switch update() between the copy-engine exchange (default: no SM time next to the SpMV kernel) and the
+  /// kernel-driven one (device-side epochs: what a captured CUDA graph can replay); returns the previous setting.
+  /// No-op (false) where the kernel exchange was not set up.  Every rank must switch at the same point, with no
+  /// update in flight.
+  bool set_kernel_exchange(bool on) const
+  {
+    const bool was = _use_kernel;
+    if (_halo_kernel)
+      _use_kernel = on;
+    return was;
   }
 
 private:
@@ -134,7 +145,9 @@ private:
   bool _halo_kernel = false;
   void* _halo_desc = nullptr;
   mutable void* _pending_tail = nullptr;
-  mutable bool _pending_on_comm = false; // ... and its push went to the side stream
+  mutable bool _use_kernel = false; // update() takes the kernel channel (B200_HALO=kernel, or spmv::cg for its solve)
+  size_t _kb_base = 0;              // the kernel channel's [slot 0 | slot 1 | flags] inside the staging buffer
+  std::vector<size_t> _peer_kb_base;
   bool _peer_ok = false;
   char* _stage = nullptr;            // my staging buffer (cudaMalloc, IPC-exported)
   size_t _slot_bytes = 0;

@@ -141,6 +141,7 @@ void L2GMap::setup_peer_halo()
     std::int64_t slot_bytes;
     std::int64_t rev_base;
     std::int64_t rev_slot_bytes;
+    std::int64_t kb_base;
     std::int64_t ok;
   };
   Card mine;
@@ -151,7 +152,11 @@ void L2GMap::setup_peer_halo()
   _rev_slot_bytes = (sizeof(double) * std::max<size_t>(_num_indices, 1) + 255) / 256 * 256;
   const size_t flag_bytes = (sizeof(std::uint32_t) * static_cast<size_t>(mpi_size) + 255) / 256 * 256;
   _rev_base = 2 * _slot_bytes + flag_bytes;
-  const size_t total = _rev_base + 2 * _rev_slot_bytes + flag_bytes + 256; // + a scratch line for the probe
+  // ... and behind those the kernel-driven exchange's own channel (slots + flags): the two forward exchanges never
+  // share a flag word or a slot, so each keeps its own epoch count (host-side for the copy-engine one, device-side
+  // for the kernel one) and they can be used in turn on one map
+  _kb_base = _rev_base + 2 * _rev_slot_bytes + flag_bytes;
+  const size_t total = _kb_base + 2 * _slot_bytes + flag_bytes + 256; // + a scratch line for the probe
   void* stage = nullptr;
   if (ok && b200_ipc_alloc(&stage, total, mine.handle) != B200_OK)
     ok = 0;
@@ -166,6 +171,7 @@ void L2GMap::setup_peer_halo()
   mine.slot_bytes = static_cast<std::int64_t>(_slot_bytes);
   mine.rev_base = static_cast<std::int64_t>(_rev_base);
   mine.rev_slot_bytes = static_cast<std::int64_t>(_rev_slot_bytes);
+  mine.kb_base = static_cast<std::int64_t>(_kb_base);
   mine.ok = ok;
 
   std::vector<Card> cards(mpi_size);
@@ -188,6 +194,7 @@ void L2GMap::setup_peer_halo()
   _peer_slot_bytes.assign(nnbr, 0);
   _peer_rev_base.assign(nnbr, 0);
   _peer_rev_slot_bytes.assign(nnbr, 0);
+  _peer_kb_base.assign(nnbr, 0);
   _land.assign(nnbr, -1);
   _rev_land.assign(nnbr, -1);
   if (ok) {
@@ -202,6 +209,7 @@ void L2GMap::setup_peer_halo()
       _peer_slot_bytes[i] = static_cast<size_t>(cards[q].slot_bytes);
       _peer_rev_base[i] = static_cast<size_t>(cards[q].rev_base);
       _peer_rev_slot_bytes[i] = static_cast<size_t>(cards[q].rev_slot_bytes);
+      _peer_kb_base[i] = static_cast<size_t>(cards[q].kb_base);
       _land[i] = land_all[static_cast<size_t>(q) * mpi_size + _mpi_rank];
       _rev_land[i] = rland_all[static_cast<size_t>(q) * mpi_size + _mpi_rank];
     }
@@ -209,24 +217,26 @@ void L2GMap::setup_peer_halo()
   int all_ok = 0;
   CHECK_MPI(MPI_Allreduce(&ok, &all_ok, 1, MPI_INT, MPI_MIN, _comm));
   _peer_ok = all_ok != 0;
-  // Kernel-driven exchange (push + wait kernels, device-side epoch; b200spmv.h): the default whenever the
-  // peers are mapped.  B200_HALO=copy keeps the copy-engine + stream-memop exchange.
-  int want_kernel = _peer_ok && nnbr >= 1 && nnbr <= B200_HALO_MAX_NEIGHBOURS && !(mode && std::strcmp(mode, "copy") == 0);
-  if (_peer_ok && nnbr == 0)
-    want_kernel = !(mode && std::strcmp(mode, "copy") == 0); // nothing to exchange: agree with the others
+  // Kernel-driven exchange (push + wait kernels, device-side epoch; b200spmv.h), on its own channel of the staging
+  // buffer.  It is what a captured CUDA graph can replay, so spmv::cg switches to it for the solve
+  // (set_kernel_exchange); plain update() calls keep the copy-engine exchange, which costs no SM time next to the
+  // persistent SpMV kernel.  B200_HALO=kernel uses it for every update, B200_HALO=copy never.
+  int want_kernel = _peer_ok && nnbr <= B200_HALO_MAX_NEIGHBOURS && !(mode && std::strcmp(mode, "copy") == 0);
   if (want_kernel && nnbr >= 1) {
     std::vector<void*> ps0(nnbr), ps1(nnbr), pf(nnbr), mf(nnbr);
     for (int i = 0; i < nnbr; ++i) {
-      ps0[i] = _peer_stage[i];
-      ps1[i] = _peer_stage[i] + _peer_slot_bytes[i];
-      pf[i] = _peer_stage[i] + 2 * _peer_slot_bytes[i] + sizeof(std::uint32_t) * _mpi_rank;
-      mf[i] = _stage + 2 * _slot_bytes + sizeof(std::uint32_t) * _neighbours[i];
+      char* pb = _peer_stage[i] + _peer_kb_base[i];
+      ps0[i] = pb;
+      ps1[i] = pb + _peer_slot_bytes[i];
+      pf[i] = pb + 2 * _peer_slot_bytes[i] + sizeof(std::uint32_t) * _mpi_rank;
+      mf[i] = _stage + _kb_base + 2 * _slot_bytes + sizeof(std::uint32_t) * _neighbours[i];
     }
     if (b200_halo_desc_create(&_halo_desc, nnbr, _recv_offset.data(), _land.data(), ps0.data(), ps1.data(), pf.data(),
-                              _stage, _stage + _slot_bytes, mf.data(), static_cast<std::int64_t>(_ghosts.size()),
-                              gpu->get_cuda_stream()) != B200_OK)
+                              _stage + _kb_base, _stage + _kb_base + _slot_bytes, mf.data(),
+                              static_cast<std::int64_t>(_ghosts.size()), gpu->get_cuda_stream()) != B200_OK)
       want_kernel = 0;
   }
+  _use_kernel = mode && std::strcmp(mode, "kernel") == 0;
   int all_kernel = 0;
   CHECK_MPI(MPI_Allreduce(&want_kernel, &all_kernel, 1, MPI_INT, MPI_MIN, _comm));
   _halo_kernel = all_kernel != 0;
@@ -388,37 +398,25 @@ void L2GMap::finish_kernel_halo() const
   if (!_pending_tail)
     return;
   const B200Executor* gpu = as_b200(_exec);
-  if (_pending_on_comm) // the push ran on the side stream: its epoch must be in place before the wait kernel reads it
-    detail::check(b200_stream_wait_event(gpu->get_cuda_stream(), gpu->arrived_event()), "stream wait");
   detail::check(halo_wait(_halo_desc, static_cast<std::int64_t>(_ghosts.size()), static_cast<T*>(_pending_tail),
                           gpu->get_cuda_stream()),
                 "halo wait + unpack");
   _pending_tail = nullptr;
-  _pending_on_comm = false;
 }
 //-----------------------------------------------------------------------------
 template <typename T>
 void L2GMap::exchange_forward(T* vec_data, bool overlap) const
 {
-  if (_halo_kernel) {
+  if (_halo_kernel && _use_kernel) {
     const B200Executor* gpu = as_b200(_exec);
     if (_neighbours.empty())
       return;
     detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
     finish_kernel_halo<T>(); // an exchange the caller never finalised: its slot must be drained before the next push
-    void* stream = gpu->get_cuda_stream();
-    if (overlap) {
-      // Overlapping models: the push goes to the side stream, behind an event that says "x is ready", so that its
-      // NVLink stores and system-scope fence run under whatever the caller enqueues next on the compute stream
-      // (Matrix::mult: the local block).  Fork and join are events, so a stream capture follows both streams.
-      detail::check(b200_event_record(gpu->packed_event(), stream), "event record");
-      detail::check(b200_stream_wait_event(gpu->comm_stream(), gpu->packed_event()), "stream wait");
-      stream = gpu->comm_stream();
-    }
-    detail::check(halo_push(_halo_desc, _num_indices, _indexbuf, vec_data, stream), "halo push");
-    if (overlap)
-      detail::check(b200_event_record(gpu->arrived_event(), stream), "event record");
-    _pending_on_comm = overlap;
+    // On the compute stream, in front of whatever the caller enqueues next: a push on the side stream can be
+    // starved by the persistent SpMV kernel (it holds every SM's registers), and then the neighbours' wait kernels
+    // stall on it -- measured: 0.28 ms per symmetric 7-point step at 8 GPUs against 0.25 with the push in line.
+    detail::check(halo_push(_halo_desc, _num_indices, _indexbuf, vec_data, gpu->get_cuda_stream()), "halo push");
     _pending_tail = vec_data + (_ranges[_mpi_rank + 1] - _ranges[_mpi_rank]);
     if (!overlap)
       finish_kernel_halo<T>();
@@ -482,7 +480,7 @@ void L2GMap::update_finalise(T*) const
   if (gpu == nullptr)
     throw std::runtime_error("L2GMap::update_finalise needs the B200 executor");
   detail::check(b200_set_device(gpu->get_device_id()), "cudaSetDevice");
-  if (_halo_kernel) {
+  if (_halo_kernel && _use_kernel) {
     finish_kernel_halo<T>();
     return;
   }

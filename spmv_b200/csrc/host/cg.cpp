@@ -199,6 +199,14 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   double *r = w.r, *Ap = w.Ap, *x_padded = w.x_padded, *p = w.p, *state = w.state, *scratch = w.scratch, *hist = w.hist;
   const int hist_len = w.hist_cap;
 
+  // the solve uses the kernel-driven halo exchange (graph-capturable); plain update() calls keep the map's default
+  struct HaloScope {
+    const L2GMap& m;
+    bool was;
+    explicit HaloScope(const L2GMap& m_) : m(m_), was(m_.set_kernel_exchange(true)) {}
+    ~HaloScope() { m.set_kernel_exchange(was); }
+  } halo_scope(*col_l2g);
+
   // the private stream starts after whatever the caller has queued on the executor's stream
   void* user_stream = exec.get_cuda_stream();
   void* stream = w.stream;

@@ -16,6 +16,7 @@
 // plain-loop restatement of daxpy/dscal.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 #include <algorithm>
@@ -491,7 +492,14 @@ int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double
     B200_REQUIRE(b >= 1, "fused CG step does not fit an SM");
     per_sm[dev] = b;
   }
-  const int grid = std::max(1, std::min(std::min(vec_grid(n), num_sms() * per_sm[dev]), DOT_PARTIALS));
+  // B200_CG_FUSED_CTAS caps the CTAs per SM (sweeps; profiles/r02_fused_probe.txt: the full co-resident grid is
+  // best at 16.8 M rows and no worse at 2.1 M)
+  static const int want_per_sm = [] {
+    const char* e = getenv("B200_CG_FUSED_CTAS");
+    return (e && *e) ? atoi(e) : 0;
+  }();
+  const int use_per_sm = want_per_sm > 0 ? std::min(per_sm[dev], want_per_sm) : per_sm[dev];
+  const int grid = std::max(1, std::min(std::min(vec_grid(n), num_sms() * use_per_sm), DOT_PARTIALS));
   PeerDesc* peer = static_cast<PeerDesc*>(peer_ctx);
   void* args[] = {&n, &d_state, &d_p, &d_Ap, &d_x, &d_r, &d_hist, &hist_len, &peer, &need_dot};
   B200_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(cg_fused_step_kernel), dim3(grid), dim3(VEC_THREADS),

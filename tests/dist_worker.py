@@ -222,9 +222,9 @@ def main():
                 continue
             inps = [cases.local_inputs(rows, N, r, size) for r in range(size)]
             plans = OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps])
-            for halo in ("peer", "nccl"):
-                if halo == "nccl":
-                    os.environ["B200_HALO"] = "nccl"
+            for halo in ("peer", "kernel", "nccl"):  # copy-engine exchange (default), kernel-driven exchange, NCCL
+                if halo != "peer":
+                    os.environ["B200_HALO"] = halo
                 inp = inps[rank]
                 A = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
                                              inp["ncols_local"], [], inp["col_ghosts"], False, api.COLLECTIVE_BLOCKING)
