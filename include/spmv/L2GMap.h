@@ -90,6 +90,8 @@ public:
   {
     return _ranges.size() <= 2 ? "none" : (_halo_kernel && _use_kernel) ? "kernel" : _peer_ok ? "copy" : "nccl";
   }
+  /// ... and the one spmv::cg switches to for its solve
+  const char* halo_mode_cg() const { return (_ranges.size() > 2 && _halo_kernel) ? "kernel" : halo_mode(); }
   /// Switch update() between the copy-engine exchange (default: no SM time next to the SpMV kernel) and the
   /// kernel-driven one (device-side epochs: what a captured CUDA graph can replay); returns the previous setting.
   /// No-op (false) where the kernel exchange was not set up.  Every rank must switch at the same point, with no

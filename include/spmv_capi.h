@@ -109,7 +109,8 @@ SPMVH_API int spmvh_cg(void* exec, void* mat, const double* d_b, double* d_x, in
  * microseconds per iteration of {halo update, local-block SpMV, halo wait + remote block, vector step}. */
 SPMVH_API int spmvh_cg_phases(void* exec, void* mat, const double* d_b, double* d_x, int kmax, double rtol,
                               double out_us[4], int* iterations);
-/* How this map moves its halo: "kernel", "copy", "nccl" or "none" (NUL-terminated into out[cap]). */
+/* How this map moves its halo, "<update()>/<inside spmv::cg>", each of "kernel", "copy", "nccl", "none"
+ * (NUL-terminated into out[cap]; e.g. "copy/kernel"). */
 SPMVH_API int spmvh_l2g_halo_mode(void* map, char* out, int cap);
 
 /* ---- PETSc binary writers (inputs for read_petsc) ---- */

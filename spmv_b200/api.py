@@ -372,8 +372,9 @@ class L2GMap:
         _ck(getattr(host_lib(), "spmvh_l2g_reverse_update_" + self._sfx(vec))(self.h, _dev_ptr(vec)))
 
     def halo_mode(self):
-        buf = C.create_string_buffer(16)
-        _ck(host_lib().spmvh_l2g_halo_mode(self.h, buf, 16))
+        """'<exchange update() uses>/<exchange spmv::cg switches to>', e.g. 'copy/kernel', 'none/none'."""
+        buf = C.create_string_buffer(32)
+        _ck(host_lib().spmvh_l2g_halo_mode(self.h, buf, 32))
         return buf.value.decode()
 
     def allreduce_sum(self, vec, nccl=False):

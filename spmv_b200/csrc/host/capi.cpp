@@ -413,7 +413,8 @@ int spmvh_cg_phases(void* exec, void* mat, const double* d_b, double* d_x, int k
 int spmvh_l2g_halo_mode(void* map, char* out, int cap)
 {
   return guarded([&] {
-    const char* m = as_map(map).halo_mode();
+    const std::string both = std::string(as_map(map).halo_mode()) + "/" + as_map(map).halo_mode_cg();
+    const char* m = both.c_str();
     std::strncpy(out, m, cap > 0 ? cap - 1 : 0);
     if (cap > 0)
       out[cap - 1] = 0;

@@ -323,3 +323,23 @@ def test_halo_data_movement_restated_equals_reference(kind, n, size):
         assert np.array_equal(rev[r], want_r[r]), r
         if size == 1:
             assert np.array_equal(rev[r], vec0[r])  # no neighbours: a no-op
+
+
+# ---- the CPU legs of bench.py (bench_cpu_legs.py): the reference's code timed on host cores.  Not timings here:
+#      that every leg runs, names its sample, and that the configs[0] loop reproduces the known final norm. ----
+@needs_ref
+def test_bench_cpu_legs_run():
+    import bench_cpu_legs as CL
+    from oracle import ref_api as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libspmv_ref.so not built")
+    c1 = CL.config1_mpi(n=100_000, ranks=2, n_apply=10)
+    assert c1["kind"] == "reference" and c1["ranks"] == 2 and c1["us_per_step"] > 0
+    c1b = CL.config1_mpi(n=100_000, ranks=1, n_apply=10)
+    assert abs(c1["final_x_norm"] - c1b["final_x_norm"]) <= 1e-12 * c1b["final_x_norm"]  # rank count changes last bits only
+    cg = CL.mpi_cg(27, False, nz=4, iters=5)
+    assert cg["iterations"] == 5 and cg["iters_per_s"] > 0
+    mp = CL.mpi_spmv(7, True, nz=8, n_apply=3)
+    assert mp["ms_per_step"] > 0 and mp["ranks"] >= 1
+    om = CL.omp_spmv(7, True, nz=4, budget_s=0.2)
+    assert om["kind"] == "reference" and om["rows"] == 256 * 256 * 4
