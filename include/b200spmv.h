@@ -237,6 +237,20 @@ B200_API int b200_halo_wait_unpack_f32(void* desc, int64_t nghosts, float* d_gho
  * *d_done_flag != 0 the kernel does nothing. */
 B200_API int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, double* d_out,
                     double* d_scratch, const double* d_done_flag, void* stream);
+/* Allocation-free variant of b200_cg_dot_f64.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  d_out[0] = sum a[i]*b[i],
+ * same kernel, grid and summation order -- the same bits -- as b200_cg_dot_f64, but the
+ * reduction scratch is a file-scope `static __device__` array of B200_DOT_SCRATCH_DOUBLES
+ * doubles (32 KiB) that every GPU loading the library holds until exit; the call itself
+ * performs no cudaMalloc / cudaFree / allocating library call (one 64-byte cudaMemsetAsync of
+ * the scratch header + one kernel launch, both in stream order).
+ * Limit: 0 <= n <= B200_CG_DOT_STATIC_MAX_N, else B200_EINVAL with a message naming the limit.
+ * All calls on a device share the one array: calls that can OVERLAP on the GPU (different
+ * streams without an ordering between them) race on it -- order them, or use b200_cg_dot_f64
+ * with one scratch per stream. */
+#define B200_CG_DOT_STATIC_MAX_N (1 << 28)
+B200_API int b200_cg_dot_static_f64(int32_t n, const double* d_a, const double* d_b, double* d_out, void* stream);
 /* st[0] = st[3] = sqrt(d_rr[0]) (d_rr = allreduced r.r, cg.cpp:47-53); clears
  * done / iteration count; stores rtol and kmax. */
 B200_API int b200_cg_init_state(double* d_state, const double* d_rr, double rtol, int32_t kmax, void* stream);

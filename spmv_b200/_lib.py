@@ -66,6 +66,7 @@ SIGNATURES = {
     "b200_halo_exchange": [_p, _int, _p, _p, _p, _p, _p, _p, _p, _int, _p],
     "b200_allreduce_sum_f64": [_p, _p, _i32, _p],
     "b200_cg_dot_f64": [_i32, _p, _p, _p, _p, _p, _p],
+    "b200_cg_dot_static_f64": [_i32, _p, _p, _p, _p],
     "b200_peer_reduce_mailbox_bytes": [_i32, _p],
     "b200_peer_reduce_create": [_p, _i32, _i32, _p, _p],
     "b200_peer_reduce_destroy": [_p],

@@ -565,3 +565,68 @@ int b200_peer_allreduce_sum_f64(void* ctx, double* d_inout, int32_t n, void* str
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------
+// Allocation-free dot product (no counterpart in the reference; added
+// for callers that may not call cudaMalloc: code under CUDA graph capture,
+// tight serving loops, harnesses that forbid it).
+//
+// Same kernels, same grid and same partial layout as b200_cg_dot_f64 -- so the same bits in
+// d_out -- but the reduction scratch (ticket counter + per-CTA hi/lo partials) is this
+// file-scope device array instead of a caller buffer: B200_DOT_SCRATCH_DOUBLES doubles =
+// 32 KiB, held by every GPU that loads the library until the process exits.
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: the
+// address each device maps it at comes from cudaGetSymbolAddress, resolved once per device with
+// that device current, and that pointer is what the kernel is given.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) double g_dot_static_scratch[B200_DOT_SCRATCH_DOUBLES];
+
+namespace
+{
+constexpr int STATIC_MAX_DEVICES = 64;
+double* g_dot_static_ptr[STATIC_MAX_DEVICES]; // per device, nullptr until resolved
+
+// -> the current device's address of g_dot_static_scratch (no allocation: the array is part of the module image)
+int dot_static_scratch(double** out)
+{
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "device ordinal beyond the static-scratch table");
+  double* p = __atomic_load_n(&g_dot_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) { // racing first calls resolve the same address twice: harmless
+    B200_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_dot_static_scratch));
+    B200_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned NULL for the static dot scratch");
+    __atomic_store_n(&g_dot_static_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return B200_OK;
+}
+} // namespace
+
+extern "C" int b200_cg_dot_static_f64(int32_t n, const double* d_a, const double* d_b, double* d_out, void* stream)
+{
+  B200_REQUIRE(n >= 0 && d_out, "bad argument");
+  if (n > B200_CG_DOT_STATIC_MAX_N) {
+    set_error("b200_cg_dot_static_f64: n = %d exceeds B200_CG_DOT_STATIC_MAX_N = %d (use b200_cg_dot_f64 with a caller "
+              "scratch for longer vectors)", (int)n, (int)B200_CG_DOT_STATIC_MAX_N);
+    return B200_EINVAL;
+  }
+  B200_REQUIRE(n == 0 || (d_a && d_b), "NULL vector");
+  if (int rc = need_gpu())
+    return rc;
+  double* scratch = nullptr;
+  if (int rc = dot_static_scratch(&scratch))
+    return rc;
+  // The array keeps whatever the last call left.  The partials are rewritten by every CTA before the last CTA
+  // reads them; the ticket counter must start at zero (a call that was aborted mid-kernel would leave it odd),
+  // so clear the 64-byte header in stream order.  A memset node, not an allocation.
+  B200_CUDA(cudaMemsetAsync(scratch, 0, 8 * sizeof(double), as_stream(stream)));
+  const int grid = std::min(vec_grid(n), B200_DOT_SCRATCH_DOUBLES - 8);
+  const bool al = ((reinterpret_cast<uintptr_t>(d_a) | reinterpret_cast<uintptr_t>(d_b)) & 15) == 0;
+  if (al)
+    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr);
+  else
+    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

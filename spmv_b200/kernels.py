@@ -83,6 +83,11 @@ def dot(a, b, out, scratch, done_flag=None):
                                 _stream()))
 
 
+def dot_static(a, b, out):
+    """b200_cg_dot_static_f64: the same dot product with the library's static device scratch (allocates nothing)."""
+    check(lib().b200_cg_dot_static_f64(a.numel(), _ptr(a), _ptr(b), _ptr(out), _stream()))
+
+
 def new_dot_scratch(device):
     return torch.zeros(DOT_SCRATCH_DOUBLES, dtype=torch.float64, device=device)
 
