@@ -520,6 +520,32 @@ def measure_cg(api, op, timer, dev, size):
                               "residual_true": rtrue, "converged": bool(len(hist) and hist[-1] / bnorm < 1e-8)}
     if not rtrue < 1e-6:
         raise RuntimeError(f"CG: true residual {rtrue} after {holder['it']} iterations")
+    if getattr(op, "symmetric", False) and size == 1:
+        # x'Ax in the symmetric SpMV's epilogue (default) against the separate dot kernel: speed and how far the
+        # residual histories part (they differ by roundings; so do two runs of symmetric storage with each other)
+        prev = os.environ.get("B200_CG_FUSED_DOT")
+        try:
+            os.environ["B200_CG_FUSED_DOT"] = "0"
+            api.cg(op.ex, op.A, b, xs, 10, 0.0)
+            ms0 = min(timer.run(lambda i: api.cg(op.ex, op.A, b, xs, iters, 0.0), 1) for _ in range(2))
+            it0, hist0 = api.cg(op.ex, op.A, b, xs, 5000, 1e-8, history=True)
+            it0b, hist0b = api.cg(op.ex, op.A, b, xs, 5000, 1e-8, history=True)
+        finally:
+            if prev is None:
+                os.environ.pop("B200_CG_FUSED_DOT", None)
+            else:
+                os.environ["B200_CG_FUSED_DOT"] = prev
+        import numpy as np
+
+        def dev(h1, h2):
+            m = min(len(h1), len(h2))
+            return float(np.max(np.abs(np.asarray(h1[:m]) - np.asarray(h2[:m])) / np.asarray(h2[:m]))) if m else None
+
+        res["fused_dot_ab"] = {"ms_per_iter_separate_dot": ms0 / iters, "ms_per_iter_epilogue_dot": res["ms_per_iter"],
+                               "iterations_separate_dot": int(it0), "iterations_epilogue_dot": int(holder["it"]),
+                               "history_max_rel_deviation": dev(hist, hist0),
+                               "history_max_rel_deviation_of_two_separate_dot_runs": dev(hist0b, hist0),
+                               "how": "B200_CG_FUSED_DOT=0 vs default; histories to rtol 1e-8 compared over their common length"}
     return res
 
 

@@ -120,6 +120,14 @@ B200_API int b200_csr_spmv_f32(void* plan, const int32_t* d_rowptr, const int32_
 B200_API int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
                           const double* d_val, const double* d_x, double* d_y,
                           double* d_dot, void* stream);
+/* Symmetric (lower + diagonal) storage, y = A x and d_dot[0] = x'Ax in the same pass.  The rows of y are
+ * incomplete while the kernel runs (transposed entries still to be scattered), the quadratic form is not:
+ * x'Ax = sum_r x_r (2 s_r - d_r x_r) with s_r = d_r x_r + sum_{c<r} a_rc x_c, the row sum the walk forms
+ * anyway.  Equals ddot(x, A x) up to roundings (symmetric storage is not bit-reproducible in the first
+ * place: csr_kernels.cpp:33-37 scatter order).  Square local block (every stored column < rows). */
+B200_API int b200_csr_symv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                          const double* d_val, const double* d_diag, const double* d_x, double* d_y,
+                          double* d_dot, void* stream);
 
 /* ---- symmetric CSR SpMV: CSRSpMV<T>::run, symmetric branch
  *      (csr_kernels.cpp:26-40; replaces csr_sym_gmem_atomics at

@@ -54,6 +54,7 @@ SIGNATURES = {
     "b200_csr_spmv_f64": [_p, _p, _p, _p, _f64, _p, _f64, _p, _p],
     "b200_csr_spmv_f32": [_p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_csr_spmv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p],
+    "b200_csr_symv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p],
     "b200_csr_symv_f64": [_p, _p, _p, _p, _p, _f64, _p, _f64, _p, _p],
     "b200_csr_symv_f32": [_p, _p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_gather_f64": [_i32, _p, _p, _p, _p],

@@ -249,6 +249,16 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     if (!env_flag("B200_CG_FUSED_DOT", mean_row > 10.0))
       single = nullptr;
   }
+  // Symmetric storage, no remote entries: x'Ax rides in the symmetric SpMV through the quadratic-form identity of
+  // b200_csr_symv_dot_f64 (rounding differs from ddot(p, Ap); symmetric storage is not bit-reproducible anyway).
+  const CSRMatrix<double>* sym_single = nullptr;
+  if (A.symmetric() && (A.remote_block() == nullptr || A.remote_block()->non_zeros() == 0))
+    sym_single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
+  if (sym_single && (sym_single->non_zeros() == 0 || sym_single->op().plan() == nullptr || sym_single->diagonal() == nullptr))
+    sym_single = nullptr;
+  if (sym_single && !env_flag("B200_CG_FUSED_DOT", true))
+    sym_single = nullptr;
+  const bool have_dot = single != nullptr || sym_single != nullptr;
   // vector half of the iteration in one cooperative launch: needs the peer mailboxes (or one rank); the
   // NCCL fallback keeps the separate kernels.  Default: on when there is more than one rank (where the
   // launch gaps between five small kernels cost more than they do at one rank); B200_CG_FUSED_VEC forces.
@@ -276,6 +286,12 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
                     "cg spmv+dot");
       mark(2);
       mark(3);
+    } else if (sym_single) {
+      detail::check(b200_csr_symv_dot_f64(sym_single->op().plan(), sym_single->rowptr(), sym_single->colind(),
+                                          sym_single->values(), sym_single->diagonal(), p, Ap, state + 1, stream),
+                    "cg symv+dot");
+      mark(2);
+      mark(3);
     } else if (phases && A.remote_block() != nullptr) { // Matrix::mult, opened up to time its parts
       A.local_block()->mult(1, p, 0, Ap);
       mark(2);
@@ -290,10 +306,10 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     }
     detail::NvtxRange nv("cg:vector step + reductions");
     if (fused_vec) {
-      detail::check(b200_cg_fused_step_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, single ? 0 : 1, stream),
+      detail::check(b200_cg_fused_step_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, have_dot ? 0 : 1, stream),
                     "cg fused step");
     } else {
-      if (!single)
+      if (!have_dot)
         detail::check(b200_cg_dot_f64(M, p, Ap, state + 1, scratch, state + 4, stream), "cg dot");
       allreduce(state + 1); // cg.cpp:65
       detail::check(b200_cg_update_xr_f64(M, state, p, Ap, x_padded, r, stream), "cg update x,r");
@@ -339,7 +355,7 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     iteration();
   bool graph_ready = false;
   if (!phases && use_graph && kmax > 1 && w.graph_mode != -2) {
-    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0);
+    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0) | (sym_single ? 4 : 0);
     graph_ready = w.graph != nullptr && w.graph_matrix == static_cast<const void*>(&A) && w.graph_mode == mode
                   && w.graph_epoch == detail::structure_epoch();
     if (!graph_ready) {

@@ -186,6 +186,35 @@ __device__ __forceinline__ T store_row(const SpmvArgs<T>& a, int r, T sum)
   return out;
 }
 
+// One row's share of x . (A x) for the DOT epilogue.
+//   general storage: x_r * out_r.
+//   symmetric (lower + diagonal) storage: out_r is incomplete when the row is walked -- the transposed
+//   entries of later rows are still to be scattered into it -- but the whole quadratic form is not:
+//     x'Ax = sum_r x_r (d_r x_r + 2 sum_{c<r} a_rc x_c) = sum_r x_r (2 s_r - d_r x_r),  s_r = the row sum just formed
+//   (alpha = 1).  dxr = d_r * x_r as the walk rounded it.  Differs from ddot(x, A x) by roundings only, which
+//   symmetric storage (unordered RED adds) does not reproduce bit for bit in the first place.
+template <typename T, bool SYM>
+__device__ __forceinline__ void dot_row(dd& dot, const SpmvArgs<T>& a, int r, T out, T xr, T dxr)
+{
+  if (SYM) {
+    // plain fp64 per thread (one FMA per row; a thread sees ~100 rows), twice the working precision only from
+    // the warp sums on: two error-free products per row cost the 7-point kernel 11 % (fp64 issue, 56-register cap)
+    dot.hi = fma((double)xr, 2.0 * (double)out - (double)dxr, dot.hi);
+  } else {
+    dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+  }
+}
+template <typename T, bool SYM>
+__device__ __forceinline__ void dot_row(dd& dot, const SpmvArgs<T>& a, int r, T out)
+{
+  if (SYM) {
+    const T xr = __ldg(a.x + r);
+    dot_row<T, SYM>(dot, a, r, out, xr, mul_rn(__ldg(a.diag + r), xr));
+  } else {
+    dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+  }
+}
+
 // Walk a tile that sits in shared memory, one thread per row.  Returns this
 // thread's share of sum_i x[i]*y[i] over the tile's rows (general storage only).
 // CHUNK entries of a row are fetched together (16 for stencil-length rows, 8 / 4
@@ -252,8 +281,12 @@ __device__ __forceinline__ dd walk_staged(const SpmvArgs<T>& a, const unsigned c
       }
     }
     const T out = store_row<T, SYM>(a, r, sum);
-    if (DOT)
-      dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+    if (DOT) {
+      if (SYM)
+        dot_row<T, SYM>(dot, a, r, out, xi, mul_rn(DX ? sd[k] : __ldg(a.diag + r), xi));
+      else
+        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+    }
   }
 
   if (LONG) {
@@ -268,7 +301,7 @@ __device__ __forceinline__ dd walk_staged(const SpmvArgs<T>& a, const unsigned c
       if (lane == 0) {
         const T out = store_row<T, SYM>(a, r, sum);
         if (DOT)
-          dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+          dot_row<T, SYM>(dot, a, r, out);
       }
     }
   }
@@ -348,8 +381,12 @@ __device__ __forceinline__ dd walk_stream(const SpmvArgs<T>& a, unsigned char* s
         red_add(a.y + sc[j], mul_rn(mul_rn(a.alpha, sv[j]), xi));
     }
     const T out = store_row<T, SYM>(a, r, sum);
-    if (DOT)
-      dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+    if (DOT) {
+      if (SYM)
+        dot_row<T, SYM>(dot, a, r, out, xi, mul_rn(sd[k], xi));
+      else
+        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+    }
   }
 
   if (LONG) {
@@ -374,7 +411,7 @@ __device__ __forceinline__ dd walk_stream(const SpmvArgs<T>& a, unsigned char* s
           part += sd[k] * xi;
         const T out = store_row<T, SYM>(a, r, part);
         if (DOT)
-          dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+          dot_row<T, SYM>(dot, a, r, out);
       }
     }
   }
@@ -396,7 +433,7 @@ __device__ __forceinline__ dd walk_direct(const SpmvArgs<T>& a, int r0, int nrow
     if (lane == 0) {
       const T out = store_row<T, SYM>(a, r, sum);
       if (DOT)
-        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+        dot_row<T, SYM>(dot, a, r, out);
     }
   }
   return dot;
@@ -453,7 +490,7 @@ __device__ __forceinline__ dd walk_direct_cta(const SpmvArgs<T>& a, int r0, int 
         tot += __ldg(a.diag + r) * xi;
       const T out = store_row<T, SYM>(a, r, tot);
       if (DOT)
-        dd_add_prod(dot, (double)__ldg(a.x + r), (double)out);
+        dot_row<T, SYM>(dot, a, r, out);
     }
     named_bar_sync(bar_id, nthreads); // s_part is free again
   }
@@ -1701,6 +1738,7 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   } else if (SYM) {
     B200_REQUIRE(d_diag != nullptr, "symmetric SpMV needs the diagonal");
     if (p.num_tiles == 0) {
+      B200_REQUIRE(d_dot == nullptr, "symmetric dot epilogue needs a block with stored entries");
       diag_only_kernel<T><<<gb, tb, 0, st>>>(p.rows, d_diag, d_x, alpha, beta, d_y);
       B200_LAUNCH_CHECK();
       return B200_OK;
@@ -1778,11 +1816,14 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
                        && (!SYM || (aligned16(d_diag) && aligned16(d_x)));
   if (p.variant == 0 && bulk_ok) {
     if (d_dot != nullptr) {
-      B200_REQUIRE((std::is_same<T, double>::value) && !SYM, "dot epilogue: general fp64 only");
+      B200_REQUIRE((std::is_same<T, double>::value), "dot epilogue: fp64 only");
+      // symmetric storage: the quadratic-form identity of dot_row() holds for y = A x only
+      B200_REQUIRE(!SYM || (alpha == T(1) && beta == T(0) && !ranged), "symmetric dot epilogue: alpha = 1, beta = 0");
       B200_REQUIRE((long long)num_sms() * p.ctas_per_sm <= p.partials_len, "partials too small");
+      constexpr bool D = !SYM || std::is_same<T, double>::value; // (no fp32 symmetric instantiation)
       if (has_long)
-        return launch_pipe_walk<T, SYM, !SYM, true>(p, a, st);
-      return launch_pipe_walk<T, SYM, !SYM, false>(p, a, st);
+        return launch_pipe_walk<T, SYM, D, true>(p, a, st);
+      return launch_pipe_walk<T, SYM, D, false>(p, a, st);
     }
     if (has_long)
       return launch_pipe_walk<T, SYM, false, true>(p, a, st);
@@ -2034,6 +2075,14 @@ int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_
   B200_REQUIRE(d_dot != nullptr, "d_dot is NULL");
   return run_spmv<double, false>(plan, d_rowptr, d_colind, d_val, nullptr, 1.0, d_x, 0.0, d_y,
                                  d_dot, stream);
+}
+
+int b200_csr_symv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                          const double* d_val, const double* d_diag, const double* d_x, double* d_y,
+                          double* d_dot, void* stream)
+{
+  B200_REQUIRE(d_dot != nullptr, "d_dot is NULL");
+  return run_spmv<double, true>(plan, d_rowptr, d_colind, d_val, d_diag, 1.0, d_x, 0.0, d_y, d_dot, stream);
 }
 
 int b200_csr_symv_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,

@@ -68,6 +68,12 @@ def symv(plan, rowptr, colind, values, diag, x, y, alpha=1.0, beta=0.0):
             _stream()))
 
 
+def symv_dot(plan, rowptr, colind, values, diag, x, y, dot):
+    """y = A x (lower + diagonal storage) and dot[0] = x'Ax in the same pass (b200_csr_symv_dot_f64)."""
+    check(lib().b200_csr_symv_dot_f64(plan.h, _ptr(rowptr), _ptr(colind), _ptr(values), _ptr(diag), _ptr(x), _ptr(y),
+                                      _ptr(dot), _stream()))
+
+
 def gather(idx, vec, out):
     f = lib().b200_gather_f32 if vec.dtype == torch.float32 else lib().b200_gather_f64
     check(f(idx.numel(), _ptr(idx), _ptr(vec), _ptr(out), _stream()))

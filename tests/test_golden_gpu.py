@@ -253,9 +253,11 @@ def test_cg_symmetric_modes(ex, monkeypatch):
     b = torch.from_numpy(b_h).cuda()
     x = torch.zeros(N, dtype=torch.float64, device="cuda")
     monkeypatch.setenv("B200_CG_GRAPH_STRICT", "1")
-    for graph, fv in ((0, 0), (1, 1), (1, 0), (0, 1)):
+    # fd: x'Ax in the symmetric SpMV's epilogue (b200_csr_symv_dot_f64) against the separate dot kernel
+    for graph, fv, fd in ((0, 0, 0), (1, 1, 0), (1, 0, 1), (0, 1, 1), (1, 1, 1), (0, 0, 1)):
         monkeypatch.setenv("B200_CG_GRAPH", str(graph))
         monkeypatch.setenv("B200_CG_FUSED_VEC", str(fv))
+        monkeypatch.setenv("B200_CG_FUSED_DOT", str(fd))
         it, hist = api.cg(ex, A, b, x, 500, 1e-10, history=True)
         assert abs(it - it_o) <= 1
         m = min(20, it, it_o)

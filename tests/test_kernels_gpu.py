@@ -261,6 +261,59 @@ def test_random_symmetric(cuda, alpha, beta):
     assert rel_l2(y, OK.symv(srp, sci, sv, d, x, alpha, beta, y0)) < TOL
 
 
+def _symv_dot_case(cuda, srp, sci, sv, d, x, tune=None):
+    n = len(d)
+    rpd, cid, vd = dev_csr(srp, sci, sv, cuda, torch.float64)
+    dd_ = torch.from_numpy(np.ascontiguousarray(d)).to(cuda)
+    xd = torch.from_numpy(np.ascontiguousarray(x)).to(cuda)
+    plan = K.CsrPlan(n, n, rpd, True, nnz=len(sv))
+    if tune:
+        plan.tune(**tune)
+    got = []
+    for _ in range(2):  # the partials / ticket of the plan are reused: twice in a row
+        y = torch.full((n,), float("nan"), dtype=torch.float64, device=cuda)
+        dot = torch.full((1,), float("nan"), dtype=torch.float64, device=cuda)
+        K.symv_dot(plan, rpd, cid, vd, dd_, xd, y, dot)
+        torch.cuda.synchronize()
+        got.append((y.cpu().numpy(), dot.item()))
+    plan.close()
+    want_y = OK.symv(srp, sci, sv, d, x)
+    # x'Ax in exact-ish arithmetic: the full operator, products summed by math.fsum
+    full = sp.csr_matrix((sv, sci, srp), shape=(n, n))
+    full = (full + full.T + sp.diags(d)).tocsr()
+    import math
+    terms = x * (full @ x)
+    want = math.fsum(terms.tolist())
+    scale = float(np.abs(full).dot(np.abs(x)) @ np.abs(x))
+    for y, dot in got:
+        assert rel_l2(y, want_y) < TOL
+        assert abs(dot - want) <= 1e-13 * max(1.0, scale), (dot, want, scale)
+    assert got[0][1] == got[1][1]  # the quadratic form is summed deterministically (y's scatter order is not)
+
+
+@pytest.mark.parametrize("tune", [None] + [t for t in VARIANTS if t["variant"] != 1])
+def test_symv_dot_laplace(cuda, tune):
+    """b200_csr_symv_dot_f64: y = A x and x'Ax in one pass, every symmetric walk (the identity of dot_row())."""
+    n1 = 24
+    N = n1 ** 3
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 7)
+    srp, sci, sv, d = split_symmetric(rp, col, val)
+    _symv_dot_case(cuda, srp, sci, sv, d, np.random.default_rng(11).standard_normal(N), tune)
+
+
+def test_symv_dot_irregular_and_long_rows(cuda):
+    n = 6000
+    rp0, col0, val0 = synth.powerlaw_rows(n, 0, n, band=512)
+    A = sp.csr_matrix((val0, col0, rp0), shape=(n, n)).tolil()
+    A[n - 1, : n - 1] = 0.25  # one row far longer than a stage: the direct CTA walk
+    A[n // 2, : n // 2: 2] = -0.5  # and one long row inside a staged tile
+    A = A.tocsr()
+    S = (A + A.T).tocsr()
+    S.sort_indices()
+    srp, sci, sv, d = split_symmetric(S.indptr, S.indices, S.data)
+    _symv_dot_case(cuda, srp, sci, sv, d, np.random.default_rng(12).standard_normal(n))
+
+
 def test_float32_twins(cuda):
     rng = np.random.default_rng(6)
     n1 = 16
