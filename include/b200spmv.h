@@ -120,6 +120,17 @@ B200_API int b200_csr_spmv_f32(void* plan, const int32_t* d_rowptr, const int32_
 B200_API int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,
                           const double* d_val, const double* d_x, double* d_y,
                           double* d_dot, void* stream);
+/* Two-block operators (local block, then remote block with beta = 1; Matrix::spmv_overlap / spmv_sym): the
+ * remote product that COMPLETES the x.(A x) epilogue.  Call b200_csr_spmv_dot_f64 (or b200_csr_symv_dot_f64) on
+ * the local block, then this on the remote block with the same x, y and d_dot on the same stream:
+ * y[r] += (remote row sum) over the block's non-empty rows, and d_dot[0] = x.(A x) over both blocks -- for a
+ * general local block the same double ddot(x, y_final) rounds to (error-free products, sums in twice the working
+ * precision, carried between the two kernels in the local plan's per-CTA partials).  The remote plan must hold a
+ * list of short non-empty rows (b200_csr_plan_rowlist_dot_ok: *ok = 1). */
+B200_API int b200_csr_plan_rowlist_dot_ok(void* plan, int32_t* ok);
+B200_API int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr,
+                                  const int32_t* d_colind, const double* d_val, const double* d_x, double* d_y,
+                                  double* d_dot, void* stream);
 /* Symmetric (lower + diagonal) storage, y = A x and d_dot[0] = x'Ax in the same pass.  The rows of y are
  * incomplete while the kernel runs (transposed entries still to be scattered), the quadratic form is not:
  * x'Ax = sum_r x_r (2 s_r - d_r x_r) with s_r = d_r x_r + sum_{c<r} a_rc x_c, the row sum the walk forms
@@ -281,6 +292,13 @@ B200_API int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r,
 B200_API int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x,
                            double* d_r, double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot,
                            void* stream);
+/* Same, and the launch also performs the PUSH half of the kernel-driven halo exchange of d_p for the next
+ * iteration (L2GMap::update(p), cg.cpp:59; b200_halo_push_f64 with halo_desc / n_idx / d_idx) once the new p is
+ * out grid-wide -- also when st[4] != 0 (p unchanged), so that every call is exactly one push.  The caller pairs
+ * it with b200_halo_wait_unpack_f64 before the next remote-block product.  halo_desc == NULL: plain fused step. */
+B200_API int b200_cg_fused_step_halo_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x,
+                                double* d_r, double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot,
+                                void* halo_desc, int32_t n_idx, const int32_t* d_idx, void* stream);
 
 /* ---- CUDA graphs: a captured sequence of the calls above replayed with one launch (the CG loop:
  *      all per-iteration state, halo epochs included, lives in device memory). ---- */

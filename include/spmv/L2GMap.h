@@ -104,6 +104,19 @@ public:
     return was;
   }
 
+  /// For a kernel that performs the PUSH half of the kernel-driven exchange itself (the fused CG step,
+  /// b200_cg_fused_step_halo_f64): the descriptor, the index list and its length; desc == nullptr unless the
+  /// kernel exchange is the active one and this rank has neighbours.
+  struct KernelPush {
+    void* desc = nullptr;
+    const std::int32_t* d_index = nullptr;
+    std::int32_t n_index = 0;
+  };
+  KernelPush kernel_push() const;
+  /// The counterpart of update(vec) after such a kernel was enqueued on the executor's stream: the exchange is
+  /// in flight, its wait + unpack follows at once (blocking models) or in update_finalise (overlapping models).
+  void adopt_pushed(double* vec_data) const;
+
 private:
   template <typename T>
   void exchange_forward(T* vec_data, bool overlap) const;

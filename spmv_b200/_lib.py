@@ -55,6 +55,8 @@ SIGNATURES = {
     "b200_csr_spmv_f32": [_p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_csr_spmv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p],
     "b200_csr_symv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "b200_csr_plan_rowlist_dot_ok": [_p, _p],
+    "b200_csr_spmv_rowlist_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p],
     "b200_csr_symv_f64": [_p, _p, _p, _p, _p, _f64, _p, _f64, _p, _p],
     "b200_csr_symv_f32": [_p, _p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_gather_f64": [_i32, _p, _p, _p, _p],
@@ -74,6 +76,7 @@ SIGNATURES = {
     "b200_peer_allreduce_sum_f64": [_p, _p, _i32, _p],
     "b200_cg_init_state": [_p, _p, _f64, _i32, _p],
     "b200_cg_fused_step_f64": [_i32, _p, _p, _p, _p, _p, _p, _i32, _p, _int, _p],
+    "b200_cg_fused_step_halo_f64": [_i32, _p, _p, _p, _p, _p, _p, _i32, _p, _int, _p, _i32, _p, _p],
     "b200_graph_capture_begin": [_p],
     "b200_graph_capture_end": [_p, C.POINTER(_p)],
     "b200_graph_launch": [_p, _p],

@@ -404,6 +404,28 @@ void L2GMap::finish_kernel_halo() const
   _pending_tail = nullptr;
 }
 //-----------------------------------------------------------------------------
+L2GMap::KernelPush L2GMap::kernel_push() const
+{
+  KernelPush k;
+  if (_halo_kernel && _use_kernel && !_neighbours.empty()) {
+    k.desc = _halo_desc;
+    k.d_index = _indexbuf;
+    k.n_index = _num_indices;
+  }
+  return k;
+}
+//-----------------------------------------------------------------------------
+void L2GMap::adopt_pushed(double* vec_data) const
+{
+  if (!(_halo_kernel && _use_kernel) || _neighbours.empty())
+    throw std::runtime_error("L2GMap::adopt_pushed: the kernel-driven exchange is not active");
+  if (_pending_tail)
+    throw std::runtime_error("L2GMap::adopt_pushed: an exchange is still waiting for its finalise");
+  _pending_tail = vec_data + (_ranges[_mpi_rank + 1] - _ranges[_mpi_rank]);
+  if (!overlapping())
+    finish_kernel_halo<double>();
+}
+//-----------------------------------------------------------------------------
 template <typename T>
 void L2GMap::exchange_forward(T* vec_data, bool overlap) const
 {

@@ -234,31 +234,45 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   allreduce(state + 2);
   detail::check(b200_cg_init_state(state, state + 2, rtol, kmax, stream), "cg init");
 
-  // fused p.Ap epilogue: single general block only.  It pays only where the SpMV instantiation keeps its
+  // fused p.Ap epilogue, general storage: it pays only where the SpMV instantiation keeps its
   // occupancy with the extra registers: stencil-length rows (16-entry walk; 27-point 256^3: 1.157 vs
   // 1.150 ms/iteration, one launch fewer).  With short rows the dot-carrying 8-entry walk loses a resident
   // CTA per SM (7-point general 256^3: 0.74 -> 0.56 ms/iteration, profiles/r01_cg_fused_dot_ab.txt).
   // B200_CG_FUSED_DOT=0/1 forces either.
-  const CSRMatrix<double>* single = nullptr;
-  if (!A.symmetric() && A.remote_block() == nullptr)
-    single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
-  if (single && (single->non_zeros() == 0 || single->op().plan() == nullptr))
-    single = nullptr;
-  if (single) {
-    const double mean_row = (double)single->non_zeros() / (double)std::max(M, 1);
-    if (!env_flag("B200_CG_FUSED_DOT", mean_row > 10.0))
-      single = nullptr;
-  }
-  // Symmetric storage, no remote entries: x'Ax rides in the symmetric SpMV through the quadratic-form identity of
+  // Symmetric storage: x'Ax rides in the symmetric SpMV through the quadratic-form identity of
   // b200_csr_symv_dot_f64 (rounding differs from ddot(p, Ap); symmetric storage is not bit-reproducible anyway).
-  const CSRMatrix<double>* sym_single = nullptr;
-  if (A.symmetric() && (A.remote_block() == nullptr || A.remote_block()->non_zeros() == 0))
-    sym_single = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
-  if (sym_single && (sym_single->non_zeros() == 0 || sym_single->op().plan() == nullptr || sym_single->diagonal() == nullptr))
-    sym_single = nullptr;
-  if (sym_single && !env_flag("B200_CG_FUSED_DOT", true))
-    sym_single = nullptr;
-  const bool have_dot = single != nullptr || sym_single != nullptr;
+  // Two blocks (local, then remote with beta = 1): the remote product completes the sum
+  // (b200_csr_spmv_rowlist_dot_f64; general storage: still the double ddot(p, Ap) rounds to).
+  const CSRMatrix<double>* single = nullptr;     // general, one block
+  const CSRMatrix<double>* sym_single = nullptr; // symmetric, no remote entries
+  const CSRMatrix<double>* dot_local = nullptr;  // two blocks: local ...
+  const CSRMatrix<double>* dot_remote = nullptr; //             ... and remote
+  {
+    const auto* loc = dynamic_cast<const CSRMatrix<double>*>(A.local_block());
+    const auto* rem = A.remote_block() ? dynamic_cast<const CSRMatrix<double>*>(A.remote_block()) : nullptr;
+    const bool rem_empty = A.remote_block() == nullptr || A.remote_block()->non_zeros() == 0;
+    const bool loc_ok = loc && loc->non_zeros() > 0 && loc->op().plan() != nullptr && (!A.symmetric() || loc->diagonal() != nullptr);
+    const double mean_row = loc ? (double)loc->non_zeros() / (double)std::max(M, 1) : 0.0;
+    const bool want = env_flag("B200_CG_FUSED_DOT", A.symmetric() || mean_row > 10.0);
+    if (loc_ok && want) {
+      if (!A.symmetric() && A.remote_block() == nullptr) {
+        single = loc;
+      } else if (A.symmetric() && rem_empty) {
+        sym_single = loc;
+      } else if (!rem_empty && rem && rem->op().plan() != nullptr && (A.symmetric() || col_l2g->overlapping())
+                 && env_flag("B200_CG_FUSED_DOT_REMOTE", M > 6000000)) {
+        // by size: where the CG vectors live in L2 across the iteration (a few million rows per GPU) the separate
+        // dot pass costs less than the epilogues do -- 2 GPUs, 2.1 M rows each: 27-point 187.6 vs 200.3 us per
+        // iteration, symmetric 7-point 102.8 vs 110.4; at 16.8 M rows each: 1145.8 vs 1142.7 and 489.9 vs 469.3
+        std::int32_t ok = 0;
+        if (b200_csr_plan_rowlist_dot_ok(rem->op().plan(), &ok) == B200_OK && ok) {
+          dot_local = loc;
+          dot_remote = rem;
+        }
+      }
+    }
+  }
+  const bool have_dot = single != nullptr || sym_single != nullptr || dot_local != nullptr;
   // vector half of the iteration in one cooperative launch: needs the peer mailboxes (or one rank); the
   // NCCL fallback keeps the separate kernels.  Default: on when there is more than one rank (where the
   // launch gaps between five small kernels cost more than they do at one rank); B200_CG_FUSED_VEC forces.
@@ -270,6 +284,14 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   const bool graphable = (std::strcmp(hm, "kernel") == 0 || std::strcmp(hm, "none") == 0) && (peer != nullptr || exec.comm_size() == 1);
   const bool use_graph = graphable && phases == nullptr && env_flag("B200_CG_GRAPH", true);
 
+  // The fused step can also carry the halo push of the NEXT iteration's update(p) (B200_CG_FUSED_PUSH=1): one
+  // launch less per iteration.  OFF by default: inside a captured graph the separate push launch costs less than
+  // the extra grid-wide hand-over + per-CTA system fences it takes in the fused kernel (2 GPUs, 27-point, 2.1 M
+  // rows per GPU: 196.4 us per iteration with the separate push, 200.8 fused; same bits).
+  const L2GMap::KernelPush kpush = (fused_vec && env_flag("B200_CG_FUSED_PUSH", false)) ? col_l2g->kernel_push() : L2GMap::KernelPush();
+  const bool fused_push = kpush.desc != nullptr;
+  bool pushed_ahead = false; // the previous iteration's fused step already pushed p
+
   // ---- one iteration, enqueued on `stream` (cg.cpp:59-85) ----
   void* ev[6] = {};
   auto mark = [&](int i) {
@@ -278,7 +300,10 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   };
   auto iteration = [&]() {
     mark(0);
-    col_l2g->update(p); // cg.cpp:59
+    if (pushed_ahead)
+      col_l2g->adopt_pushed(p);
+    else
+      col_l2g->update(p); // cg.cpp:59
     mark(1);
     if (single) { // cg.cpp:60-63
       detail::check(b200_csr_spmv_dot_f64(single->op().plan(), single->rowptr(), single->colind(), single->values(), p,
@@ -291,6 +316,21 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
                                           sym_single->values(), sym_single->diagonal(), p, Ap, state + 1, stream),
                     "cg symv+dot");
       mark(2);
+      mark(3);
+    } else if (dot_local) {
+      if (A.symmetric())
+        detail::check(b200_csr_symv_dot_f64(dot_local->op().plan(), dot_local->rowptr(), dot_local->colind(),
+                                            dot_local->values(), dot_local->diagonal(), p, Ap, state + 1, stream),
+                      "cg symv+dot (local block)");
+      else
+        detail::check(b200_csr_spmv_dot_f64(dot_local->op().plan(), dot_local->rowptr(), dot_local->colind(),
+                                            dot_local->values(), p, Ap, state + 1, stream),
+                      "cg spmv+dot (local block)");
+      mark(2);
+      col_l2g->update_finalise(p);
+      detail::check(b200_csr_spmv_rowlist_dot_f64(dot_remote->op().plan(), dot_local->op().plan(), dot_remote->rowptr(),
+                                                  dot_remote->colind(), dot_remote->values(), p, Ap, state + 1, stream),
+                    "cg remote block + dot");
       mark(3);
     } else if (phases && A.remote_block() != nullptr) { // Matrix::mult, opened up to time its parts
       A.local_block()->mult(1, p, 0, Ap);
@@ -306,8 +346,10 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     }
     detail::NvtxRange nv("cg:vector step + reductions");
     if (fused_vec) {
-      detail::check(b200_cg_fused_step_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, have_dot ? 0 : 1, stream),
+      detail::check(b200_cg_fused_step_halo_f64(M, state, p, Ap, x_padded, r, hist, hist_len, peer, have_dot ? 0 : 1,
+                                                kpush.desc, kpush.n_index, kpush.d_index, stream),
                     "cg fused step");
+      pushed_ahead = fused_push;
     } else {
       if (!have_dot)
         detail::check(b200_cg_dot_f64(M, p, Ap, state + 1, scratch, state + 4, stream), "cg dot");
@@ -355,7 +397,7 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     iteration();
   bool graph_ready = false;
   if (!phases && use_graph && kmax > 1 && w.graph_mode != -2) {
-    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0) | (sym_single ? 4 : 0);
+    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0) | (sym_single ? 4 : 0) | (fused_push ? 8 : 0) | (dot_local ? 16 : 0);
     graph_ready = w.graph != nullptr && w.graph_matrix == static_cast<const void*>(&A) && w.graph_mode == mode
                   && w.graph_epoch == detail::structure_epoch();
     if (!graph_ready) {
@@ -417,6 +459,11 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
       detail::check(b200_memcpy_d2h_async(&w.h_flags[slot], state + 4, sizeof(Flags), stream), "flag copy");
       detail::check(b200_event_record(w.events[slot], stream), "event record");
     }
+  }
+  if (pushed_ahead) { // the last fused step pushed a halo nobody multiplies with: drain it (every rank does)
+    col_l2g->adopt_pushed(p);
+    col_l2g->update_finalise(p);
+    pushed_ahead = false;
   }
   detail::check(b200_memcpy_d2h_async(&last, state + 4, sizeof(Flags), stream), "flag copy");
   detail::check(b200_stream_synchronize(stream), "cg sync");

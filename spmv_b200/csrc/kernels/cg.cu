@@ -310,15 +310,53 @@ __device__ __forceinline__ double fused_grid_allreduce(dd v, double* st, PeerDes
   return out;
 }
 
+// The push half of the kernel-driven halo (halo.cu: halo_push_kernel) from inside the fused step: pack AND send
+// x[idx[k]] into the neighbours' staging slots over NVLink; the last CTA to finish publishes the epoch.
+// x was written by this grid: the loads go to L2 (ld.cg), never through a stale L1 line.
+__device__ __forceinline__ void fused_halo_push(HaloDesc* d, int n, const int32_t* __restrict__ idx, const double* x)
+{
+  __shared__ bool s_last;
+  const unsigned int epoch = d->epoch + 1; // advanced by the last CTA only after everybody's ticket: all read the same
+  const int slot = (int)(epoch & 1u), nnbr = d->nnbr;
+  const int stride = gridDim.x * blockDim.x;
+  int i = 0;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+    while (k >= d->send_off[i + 1])
+      ++i;
+    double* dst = reinterpret_cast<double*>(d->peer_slot[slot][i]) + d->land[i] + (k - d->send_off[i]);
+    *dst = __ldcg(x + __ldg(idx + k));
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    s_last = atomicAdd(&d->ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence_system();
+    if ((int)threadIdx.x < nnbr)
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(d->peer_flag[threadIdx.x]), "r"(epoch) : "memory");
+    if (threadIdx.x == 0) {
+      d->ticket = 0u;
+      d->epoch = epoch;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(VEC_THREADS)
     cg_fused_step_kernel(int n, double* __restrict__ st, double* __restrict__ p, const double* __restrict__ Ap,
                          double* __restrict__ x, double* __restrict__ r, double* __restrict__ hist, int hist_len,
-                         PeerDesc* peer, int need_dot)
+                         PeerDesc* peer, int need_dot, HaloDesc* halo, int n_idx, const int32_t* __restrict__ idx)
 {
   __shared__ double s_warp[2 * (VEC_THREADS / 32)];
   __shared__ double s_bcast;
-  if (st[ST_DONE] != 0.0)
-    return; // every CTA sees the same flag: it only changes at the very end of a launch
+  if (st[ST_DONE] != 0.0) {
+    // every CTA sees the same flag: it only changes at the very end of a launch.  The halo of the next
+    // iteration still goes out (p unchanged): every iteration, live or not, is one push and one wait on every rank.
+    if (halo != nullptr)
+      fused_halo_push(halo, n_idx, idx, p);
+    return;
+  }
   // read before anybody can pass the first hand-over (which needs all CTAs to have arrived)
   const unsigned int gen0 = *reinterpret_cast<volatile unsigned int*>(st + ST_GEN);
   const double rnorm_old = st[ST_RNORM_OLD], rnorm0 = st[ST_RNORM0], rtol = st[ST_RTOL];
@@ -401,6 +439,13 @@ __global__ void __launch_bounds__(VEC_THREADS)
     if (converged || iter >= (int)st[ST_KMAX])
       st[ST_DONE] = 1.0;
   }
+  if (halo != nullptr) {
+    // L2GMap::update(p) of the NEXT iteration (cg.cpp:59), here instead of in a launch of its own: one more
+    // grid-wide hand-over (every CTA's share of the new p is out), then the boundary entries go to the neighbours.
+    const dd zero = {0.0, 0.0};
+    (void)fused_grid_allreduce(zero, st, nullptr, gen0 + 3, s_warp, &s_bcast);
+    fused_halo_push(halo, n_idx, idx, p);
+  }
 }
 
 static int need_gpu()
@@ -477,6 +522,15 @@ int b200_cg_update_p_f64(int32_t n, double* d_state, const double* d_r, double* 
 int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x, double* d_r,
                            double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot, void* stream)
 {
+  return b200_cg_fused_step_halo_f64(n, d_state, d_p, d_Ap, d_x, d_r, d_hist, hist_len, peer_ctx, need_dot, nullptr, 0,
+                                     nullptr, stream);
+}
+
+int b200_cg_fused_step_halo_f64(int32_t n, double* d_state, double* d_p, const double* d_Ap, double* d_x, double* d_r,
+                                double* d_hist, int32_t hist_len, void* peer_ctx, int need_dot, void* halo_desc,
+                                int32_t n_idx, const int32_t* d_idx, void* stream)
+{
+  B200_REQUIRE(halo_desc == nullptr || (n_idx >= 0 && (n_idx == 0 || d_idx != nullptr)), "halo push: bad index list");
   B200_REQUIRE(n >= 0 && d_state, "bad argument");
   B200_REQUIRE(n == 0 || (d_p && d_Ap && d_x && d_r), "NULL vector");
   if (int rc = need_gpu())
@@ -501,7 +555,8 @@ int b200_cg_fused_step_f64(int32_t n, double* d_state, double* d_p, const double
   const int use_per_sm = want_per_sm > 0 ? std::min(per_sm[dev], want_per_sm) : per_sm[dev];
   const int grid = std::max(1, std::min(std::min(vec_grid(n), num_sms() * use_per_sm), DOT_PARTIALS));
   PeerDesc* peer = static_cast<PeerDesc*>(peer_ctx);
-  void* args[] = {&n, &d_state, &d_p, &d_Ap, &d_x, &d_r, &d_hist, &hist_len, &peer, &need_dot};
+  HaloDesc* halo = static_cast<HaloDesc*>(halo_desc);
+  void* args[] = {&n, &d_state, &d_p, &d_Ap, &d_x, &d_r, &d_hist, &hist_len, &peer, &need_dot, &halo, &n_idx, &d_idx};
   B200_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(cg_fused_step_kernel), dim3(grid), dim3(VEC_THREADS),
                                         args, 0, as_stream(stream)));
   return B200_OK;

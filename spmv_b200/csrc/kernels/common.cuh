@@ -308,4 +308,19 @@ __device__ __forceinline__ void red_add(float* addr, float v)
 }
 #endif
 
+// Descriptor of the kernel-driven peer halo (halo.cu; b200_halo_desc_create), in device memory.
+struct HaloDesc {
+  int nnbr;
+  unsigned int epoch;  // pushes completed
+  unsigned int ticket; // last-CTA-done counter of the push
+  int pad;
+  long long nghosts;
+  int send_off[B200_HALO_MAX_NEIGHBOURS + 1];       // my packed slices, neighbour by neighbour (elements)
+  long long land[B200_HALO_MAX_NEIGHBOURS];         // element offset of my slice in the neighbour's slot
+  char* peer_slot[2][B200_HALO_MAX_NEIGHBOURS];     // the neighbour's staging slots, mapped here
+  unsigned int* peer_flag[B200_HALO_MAX_NEIGHBOURS]; // my flag word in the neighbour's buffer
+  unsigned int* my_flag[B200_HALO_MAX_NEIGHBOURS];   // the neighbour's flag word in my buffer
+  char* my_slot[2];
+};
+
 } // namespace b200

@@ -90,19 +90,7 @@ static int run_scatter_add(int32_t n, const int32_t* d_idx, const T* d_in, T* d_
 // Two slots by epoch parity are enough: a neighbour's push of epoch e+1 is stream-ordered
 // after its wait for my push of epoch e, which follows my unpack of epoch e-1.
 // ---------------------------------------------------------------------------
-struct HaloDesc {
-  int nnbr;
-  unsigned int epoch;  // pushes completed
-  unsigned int ticket; // last-CTA-done counter of the push kernel
-  int pad;
-  long long nghosts;
-  int send_off[B200_HALO_MAX_NEIGHBOURS + 1];       // my packed slices, neighbour by neighbour (elements)
-  long long land[B200_HALO_MAX_NEIGHBOURS];         // element offset of my slice in the neighbour's slot
-  char* peer_slot[2][B200_HALO_MAX_NEIGHBOURS];     // the neighbour's staging slots, mapped here
-  unsigned int* peer_flag[B200_HALO_MAX_NEIGHBOURS]; // my flag word in the neighbour's buffer
-  unsigned int* my_flag[B200_HALO_MAX_NEIGHBOURS];   // the neighbour's flag word in my buffer
-  char* my_slot[2];
-};
+// (struct HaloDesc: common.cuh -- the fused CG step of cg.cu pushes through it too)
 
 template <typename T>
 __global__ void __launch_bounds__(256) halo_push_kernel(HaloDesc* d, int n, const int32_t* __restrict__ idx,

@@ -915,9 +915,12 @@ __global__ void __launch_bounds__((CW + 1) * 32) spmv_pipe_kernel(const SpmvArgs
 
   if (warp == CW) {
     if (lane == 0) {
-      const uint64_t pol_stream = SYM ? l2_policy_evict_first() : 0ull;
+      // general storage: evict_first only on request (flags bit 2; run_spmv sets it for blocks small enough that
+      // the caller's vectors can live in L2 across SpMVs if the matrix stream does not sweep them out)
+      const bool hint = SYM || (a.flags & 4);
+      const uint64_t pol_stream = hint ? l2_policy_evict_first() : 0ull;
       auto stream_g2s = [&](void* d, const void* g, uint32_t bytes, uint64_t* bar) {
-        if constexpr (SYM)
+        if (hint)
           bulk_g2s_hint(d, g, bytes, bar, pol_stream);
         else
           bulk_g2s(d, g, bytes, bar);
@@ -1310,6 +1313,86 @@ __global__ void spmv_rowlist_mixed_kernel(int n, const int32_t* __restrict__ row
     part = warp_sum(part);
     if (lane == 0)
       y[qr] = add_rn(mul_rn(alpha, part), mul_rn(beta, y[qr]));
+  }
+}
+
+// The remote block of a two-block operator with the x.(A x) epilogue COMPLETED (fp64, alpha = beta = 1):
+// y[r] += sum_j val[j] x[col[j]] over the listed rows as spmv_rowlist_kernel (same roundings), and
+//   dot_out[0] = round( B + sum_listed c_r ),
+//   B   = the double-double sum the LOCAL block's dot epilogue left as per-CTA partials in its plan
+//         (nbase pairs: hi at base[i], lo at base[base_plen + i]);
+//   c_r = x_r * y_new[r] - x_r * y_old[r]   general storage: the local epilogue counted x_r * y_old[r], and with
+//         error-free products summed in twice the working precision the total is sum_r x_r * y_final[r] to
+//         ~1e-32 -- the same double a single dot product over the final y rounds to;
+//   c_r = x_r * (row sum)                   symmetric local block (its epilogue holds x'A_local x already).
+template <bool SYMLOCAL>
+__global__ void __launch_bounds__(128)
+    spmv_rowlist_dot_kernel(int n, const int32_t* __restrict__ rowlist, const int32_t* __restrict__ rowptr,
+                            const int32_t* __restrict__ colind, const double* __restrict__ val,
+                            const double* __restrict__ x, double* __restrict__ y, const double* __restrict__ base,
+                            int base_plen, int nbase, double* __restrict__ part, int plen, unsigned int* counter,
+                            double* __restrict__ dot_out)
+{
+  __shared__ double s_warp[2 * 4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  dd dot = {0.0, 0.0};
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const int r = __ldg(rowlist + k);
+    const int rs = __ldg(rowptr + r), re = __ldg(rowptr + r + 1);
+    double sum = 0;
+    for (int j = rs; j < re; ++j)
+      sum = add_rn(sum, mul_rn(__ldg(val + j), __ldg(x + __ldg(colind + j))));
+    const double yo = y[r];
+    const double yn = add_rn(sum, yo);
+    y[r] = yn;
+    const double xr = __ldg(x + r);
+    if (SYMLOCAL) {
+      dd_add_prod(dot, xr, sum);
+    } else {
+      dd_add_prod(dot, xr, yn);
+      dd_add_prod(dot, -xr, yo);
+    }
+  }
+  dot = dd_warp_sum(dot);
+  if (lane == 0) {
+    s_warp[2 * warp] = dot.hi;
+    s_warp[2 * warp + 1] = dot.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < 4 ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < 4 ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    unsigned int ticket = 0;
+    if (lane == 0) {
+      part[blockIdx.x] = t.hi;
+      part[plen + blockIdx.x] = t.lo;
+      __threadfence();
+      ticket = atomicAdd(counter, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) {
+      __threadfence();
+      dd s = {0.0, 0.0};
+      for (int i = lane; i < nbase; i += 32) {
+        dd w;
+        w.hi = __ldcg(base + i);
+        w.lo = __ldcg(base + base_plen + i);
+        s = dd_merge(s, w);
+      }
+      for (int i = lane; i < (int)gridDim.x; i += 32) {
+        dd w;
+        w.hi = __ldcg(part + i);
+        w.lo = __ldcg(part + plen + i);
+        s = dd_merge(s, w);
+      }
+      s = dd_warp_sum(s);
+      if (lane == 0) {
+        dot_out[0] = __dadd_rn(s.hi, s.lo);
+        *counter = 0u;
+      }
+    }
   }
 }
 
@@ -1800,7 +1883,14 @@ static int run_spmv(void* plan_v, const int32_t* d_rowptr, const int32_t* d_coli
   {
     static const int seg_ef = env_int("B200_SPMV_SEG_EVICT_FIRST", 0);
     static const int contig = env_int("B200_SPMV_TILE_CONTIG", 0);
-    a.flags = (seg_ef ? 1 : 0) | (contig ? 2 : 0);
+    // B200_SPMV_STREAM_EVICT_FIRST: -1 (default) by size -- general blocks of at most B200_SPMV_L2_ROWS rows
+    // (default 6 M); 0 / 1 force.  CG on the 27-point operator, one B200, us per iteration without / with:
+    // 2.1 M rows 158.7 / 147.0, 4.2 M 294.6 / 283.6, 8.4 M 572.2 / 574.3, 16.8 M 1114 / 1125 (the five CG vectors
+    // of 2.1 M rows are 84 MB of the 126 MB L2; at 4.2 M part of them still survives the matrix stream)
+    static const int gen_ef = env_int("B200_SPMV_STREAM_EVICT_FIRST", -1);
+    static const int l2_rows = env_int("B200_SPMV_L2_ROWS", 6000000);
+    const bool ef = gen_ef >= 0 ? gen_ef != 0 : (!SYM && p.rows <= l2_rows);
+    a.flags = (seg_ef ? 1 : 0) | (contig ? 2 : 0) | (ef ? 4 : 0);
   }
   a.tile0 = ranged ? tile_begin : 0;
   a.num_tiles = ranged ? tile_end : p.num_tiles;
@@ -2075,6 +2165,44 @@ int b200_csr_spmv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_
   B200_REQUIRE(d_dot != nullptr, "d_dot is NULL");
   return run_spmv<double, false>(plan, d_rowptr, d_colind, d_val, nullptr, 1.0, d_x, 0.0, d_y,
                                  d_dot, stream);
+}
+
+int b200_csr_plan_rowlist_dot_ok(void* plan, int32_t* ok)
+{
+  B200_REQUIRE(plan != nullptr && ok != nullptr, "NULL argument");
+  const Plan& p = *static_cast<const Plan*>(plan);
+  *ok = (!p.symmetric && p.d_rowlist != nullptr && p.n_rowlist > 0 && p.max_row_len <= SHORT_ROW && p.d_partials != nullptr) ? 1 : 0;
+  return B200_OK;
+}
+
+int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr, const int32_t* d_colind,
+                                  const double* d_val, const double* d_x, double* d_y, double* d_dot, void* stream)
+{
+  B200_REQUIRE(remote_plan && local_plan && d_dot, "NULL argument");
+  const Plan& p = *static_cast<const Plan*>(remote_plan);
+  const Plan& l = *static_cast<const Plan*>(local_plan);
+  B200_REQUIRE(!p.symmetric && p.d_rowlist != nullptr && p.n_rowlist > 0 && p.max_row_len <= SHORT_ROW,
+               "rowlist dot: the block needs a row list of short rows (b200_csr_plan_rowlist_dot_ok)");
+  B200_REQUIRE(d_rowptr && d_colind && d_val && d_x && d_y, "NULL array");
+  B200_REQUIRE(l.num_tiles > 0 && l.variant == 0 && l.d_partials != nullptr, "rowlist dot: the local plan ran no dot epilogue");
+  if (num_sms() <= 0) {
+    set_error("no CUDA device available: this build has no CPU path");
+    return B200_ECUDA;
+  }
+  // the grid the local block's pipeline kernel was launched with (launch_pipe): that many partials are live
+  const int nbase = (int)std::min<long long>(l.num_tiles, (long long)num_sms() * l.ctas_per_sm);
+  B200_REQUIRE(nbase <= l.partials_len, "partials too small");
+  const int n = p.n_rowlist;
+  const int grid = std::max(1, std::min((n + 127) / 128, p.partials_len));
+  cudaStream_t st = as_stream(stream);
+  if (l.symmetric)
+    spmv_rowlist_dot_kernel<true><<<grid, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x, d_y, l.d_partials,
+                                                        l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot);
+  else
+    spmv_rowlist_dot_kernel<false><<<grid, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x, d_y, l.d_partials,
+                                                         l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
 }
 
 int b200_csr_symv_dot_f64(void* plan, const int32_t* d_rowptr, const int32_t* d_colind,

@@ -74,6 +74,18 @@ def symv_dot(plan, rowptr, colind, values, diag, x, y, dot):
                                       _ptr(dot), _stream()))
 
 
+def plan_rowlist_dot_ok(plan):
+    ok = C.c_int32(0)
+    check(lib().b200_csr_plan_rowlist_dot_ok(plan.h, C.byref(ok)))
+    return bool(ok.value)
+
+
+def spmv_rowlist_dot(remote_plan, local_plan, rowptr, colind, values, x, y, dot):
+    """Remote block (beta = 1) completing the x.(A x) epilogue the local block's spmv_dot / symv_dot started."""
+    check(lib().b200_csr_spmv_rowlist_dot_f64(remote_plan.h, local_plan.h, _ptr(rowptr), _ptr(colind), _ptr(values),
+                                              _ptr(x), _ptr(y), _ptr(dot), _stream()))
+
+
 def gather(idx, vec, out):
     f = lib().b200_gather_f32 if vec.dtype == torch.float32 else lib().b200_gather_f64
     check(f(idx.numel(), _ptr(idx), _ptr(vec), _ptr(out), _stream()))

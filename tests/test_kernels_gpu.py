@@ -314,6 +314,67 @@ def test_symv_dot_irregular_and_long_rows(cuda):
     _symv_dot_case(cuda, srp, sci, sv, d, np.random.default_rng(12).standard_normal(n))
 
 
+@pytest.mark.parametrize("symmetric", [False, True])
+def test_two_block_dot_epilogue(cuda, symmetric):
+    """Local block with the dot epilogue, then b200_csr_spmv_rowlist_dot_f64 on the remote block: y as the two plain
+    products give it, and the dot -- general storage -- the very double the Dot2 kernel returns for (x, y_final)."""
+    n1 = 20
+    M = n1 ** 3
+    ghosts = 2 * n1 * n1
+    rng = np.random.default_rng(21)
+    rp, col, val = synth.laplace3d_rows(n1, n1, n1, 0, n1, 27)
+    # remote block: the first and last plane couple to one ghost plane each, 9 entries per row
+    rrow = np.concatenate([np.arange(n1 * n1), np.arange(M - n1 * n1, M)])
+    rr = np.repeat(rrow, 9)
+    rc = M + rng.integers(0, ghosts, size=len(rr))
+    order = np.lexsort((rc, rr))
+    rr, rc = rr[order], rc[order]
+    keep = np.ones(len(rr), bool)
+    keep[1:] = (rr[1:] != rr[:-1]) | (rc[1:] != rc[:-1])
+    rr, rc = rr[keep], rc[keep]
+    rv = rng.standard_normal(len(rr))
+    rrp = np.zeros(M + 1, np.int64)
+    np.cumsum(np.bincount(rr, minlength=M), out=rrp[1:])
+    x = rng.standard_normal(M + ghosts)
+    xd = torch.from_numpy(x).to(cuda)
+    r_rp, r_ci, r_v = dev_csr(rrp, rc, rv, cuda, torch.float64)
+    rplan = K.CsrPlan(M, M + ghosts, r_rp, False, nnz=len(rv))
+    assert K.plan_rowlist_dot_ok(rplan)
+    y = torch.full((M,), float("nan"), dtype=torch.float64, device=cuda)
+    y_plain = torch.full((M,), float("nan"), dtype=torch.float64, device=cuda)
+    dot = torch.full((1,), float("nan"), dtype=torch.float64, device=cuda)
+    if symmetric:
+        srp, sci, sv, d = split_symmetric(rp, col, val)
+        l_rp, l_ci, l_v = dev_csr(srp, sci, sv, cuda, torch.float64)
+        dd_ = torch.from_numpy(d).to(cuda)
+        lplan = K.CsrPlan(M, M, l_rp, True, nnz=len(sv))
+        local = lambda out, dt: (K.symv_dot(lplan, l_rp, l_ci, l_v, dd_, xd, out, dt) if dt is not None  # noqa: E731
+                                 else K.symv(lplan, l_rp, l_ci, l_v, dd_, xd, out))
+    else:
+        l_rp, l_ci, l_v = dev_csr(rp, col, val, cuda, torch.float64)
+        lplan = K.CsrPlan(M, M, l_rp, False)
+        local = lambda out, dt: (K.spmv_dot(lplan, l_rp, l_ci, l_v, xd, out, dt) if dt is not None  # noqa: E731
+                                 else K.spmv(lplan, l_rp, l_ci, l_v, xd, out))
+    for _ in range(2):
+        local(y, dot)
+        K.spmv_rowlist_dot(rplan, lplan, r_rp, r_ci, r_v, xd, y, dot)
+        local(y_plain, None)
+        K.spmv(rplan, r_rp, r_ci, r_v, xd, y_plain, 1.0, 1.0)
+        torch.cuda.synchronize()
+        want = torch.zeros(1, dtype=torch.float64, device=cuda)
+        K.dot(xd[:M], y, want, K.new_dot_scratch(cuda))
+        torch.cuda.synchronize()
+        if symmetric:
+            assert rel_l2(y.cpu().numpy(), y_plain.cpu().numpy()) < TOL
+            scale = float(np.abs(x[:M]) @ np.abs(y.cpu().numpy()))
+            assert abs(dot.item() - want.item()) <= 1e-13 * scale
+        else:
+            assert torch.equal(y, y_plain)
+            assert dot.item() == want.item()
+    rplan.close()
+    lplan.close()
+
+
 def test_float32_twins(cuda):
     rng = np.random.default_rng(6)
     n1 = 16
