@@ -131,6 +131,14 @@ B200_API int b200_csr_plan_rowlist_dot_ok(void* plan, int32_t* ok);
 B200_API int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr,
                                   const int32_t* d_colind, const double* d_val, const double* d_x, double* d_y,
                                   double* d_dot, void* stream);
+/* Same, optionally also (peer_ctx != NULL) summing d_dot[0] over the ranks in the kernel's tail (the MPI_Allreduce
+ * of cg.cpp:65; b200_peer_reduce_create) and (halo_desc != NULL) acting as the WAIT half of the kernel-driven halo
+ * exchange in place of b200_halo_wait_unpack_f64: the kernel polls the neighbours' flags itself and reads the
+ * ghost entries of x (columns >= ghost_base = the map's local size) straight from the staging slot; the ghost
+ * tail of d_x is then left untouched. */
+B200_API int b200_csr_spmv_rowlist_dot_halo_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr,
+                                       const int32_t* d_colind, const double* d_val, const double* d_x, double* d_y,
+                                       double* d_dot, void* peer_ctx, void* halo_desc, int32_t ghost_base, void* stream);
 /* Symmetric (lower + diagonal) storage, y = A x and d_dot[0] = x'Ax in the same pass.  The rows of y are
  * incomplete while the kernel runs (transposed entries still to be scattered), the quadratic form is not:
  * x'Ax = sum_r x_r (2 s_r - d_r x_r) with s_r = d_r x_r + sum_{c<r} a_rc x_c, the row sum the walk forms
@@ -270,6 +278,14 @@ B200_API int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, do
  * with one scratch per stream. */
 #define B200_CG_DOT_STATIC_MAX_N (1 << 28)
 B200_API int b200_cg_dot_static_f64(int32_t n, const double* d_a, const double* d_b, double* d_out, void* stream);
+/* b200_cg_dot_f64 / b200_cg_update_xr_f64 with the sum over the ranks (the MPI_Allreduce of cg.cpp:65,75) in the
+ * tail of the same kernel: the last CTA to finish exchanges the folded sum over the peer mailboxes
+ * (peer_ctx: b200_peer_reduce_create; NULL: the plain kernel) and stores the global value, every rank the same bits.
+ * One launch instead of two per reduction.  Every rank of the communicator must make the call. */
+B200_API int b200_cg_dot_peer_f64(int32_t n, const double* d_a, const double* d_b, double* d_out, double* d_scratch,
+                         const double* d_done_flag, void* peer_ctx, void* stream);
+B200_API int b200_cg_update_xr_peer_f64(int32_t n, double* d_state, const double* d_p, const double* d_Ap,
+                               double* d_x, double* d_r, void* peer_ctx, void* stream);
 /* st[0] = st[3] = sqrt(d_rr[0]) (d_rr = allreduced r.r, cg.cpp:47-53); clears
  * done / iteration count; stores rtol and kmax. */
 B200_API int b200_cg_init_state(double* d_state, const double* d_rr, double rtol, int32_t kmax, void* stream);

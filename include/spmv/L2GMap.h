@@ -116,6 +116,12 @@ public:
   /// The counterpart of update(vec) after such a kernel was enqueued on the executor's stream: the exchange is
   /// in flight, its wait + unpack follows at once (blocking models) or in update_finalise (overlapping models).
   void adopt_pushed(double* vec_data) const;
+  /// For a kernel that performs the WAIT half itself (b200_csr_spmv_rowlist_dot_halo_f64 reads the ghost values
+  /// from the staging slot): the descriptor of the exchange in flight, or nullptr if none is (blocking models,
+  /// other exchange modes).  finalised_by_kernel() then stands in for update_finalise(): the ghost tail of the
+  /// vector is NOT filled.
+  void* kernel_wait_desc() const { return (_halo_kernel && _use_kernel && _pending_tail) ? _halo_desc : nullptr; }
+  void finalised_by_kernel() const { _pending_tail = nullptr; }
 
 private:
   template <typename T>

@@ -57,6 +57,7 @@ SIGNATURES = {
     "b200_csr_symv_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p],
     "b200_csr_plan_rowlist_dot_ok": [_p, _p],
     "b200_csr_spmv_rowlist_dot_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "b200_csr_spmv_rowlist_dot_halo_f64": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p],
     "b200_csr_symv_f64": [_p, _p, _p, _p, _p, _f64, _p, _f64, _p, _p],
     "b200_csr_symv_f32": [_p, _p, _p, _p, _p, _f32, _p, _f32, _p, _p],
     "b200_gather_f64": [_i32, _p, _p, _p, _p],
@@ -69,6 +70,7 @@ SIGNATURES = {
     "b200_halo_exchange": [_p, _int, _p, _p, _p, _p, _p, _p, _p, _int, _p],
     "b200_allreduce_sum_f64": [_p, _p, _i32, _p],
     "b200_cg_dot_f64": [_i32, _p, _p, _p, _p, _p, _p],
+    "b200_cg_dot_peer_f64": [_i32, _p, _p, _p, _p, _p, _p, _p],
     "b200_cg_dot_static_f64": [_i32, _p, _p, _p, _p],
     "b200_peer_reduce_mailbox_bytes": [_i32, _p],
     "b200_peer_reduce_create": [_p, _i32, _i32, _p, _p],
@@ -88,6 +90,7 @@ SIGNATURES = {
     "b200_halo_wait_unpack_f64": [_p, _i64, _p, _p],
     "b200_halo_wait_unpack_f32": [_p, _i64, _p, _p],
     "b200_cg_update_xr_f64": [_i32, _p, _p, _p, _p, _p, _p],
+    "b200_cg_update_xr_peer_f64": [_i32, _p, _p, _p, _p, _p, _p, _p],
     "b200_cg_update_p_f64": [_i32, _p, _p, _p, _p, _i32, _p],
     "b200_gen_laplace3d_rowptr": [_int, _int, _i64, _i64, _i64, _int, _int, _p, _p,
                                   C.POINTER(_i64), C.POINTER(_i64), _p],

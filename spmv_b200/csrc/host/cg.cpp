@@ -233,6 +233,11 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   detail::check(b200_cg_dot_f64(M, r, r, state + 2, scratch, nullptr, stream), "cg dot");
   allreduce(state + 2);
   detail::check(b200_cg_init_state(state, state + 2, rtol, kmax, stream), "cg init");
+  const bool timeline = env_flag("B200_CG_TIMELINE", false); // debug: phase stamps of the fused step (st[9..15])
+  {
+    static const double on = 1.0, off = 0.0;
+    detail::check(b200_memcpy_h2d_async(state + 9, timeline ? &on : &off, sizeof(double), stream), "timeline flag");
+  }
 
   // fused p.Ap epilogue, general storage: it pays only where the SpMV instantiation keeps its
   // occupancy with the extra registers: stencil-length rows (16-entry walk; 27-point 256^3: 1.157 vs
@@ -260,10 +265,9 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
       } else if (A.symmetric() && rem_empty) {
         sym_single = loc;
       } else if (!rem_empty && rem && rem->op().plan() != nullptr && (A.symmetric() || col_l2g->overlapping())
-                 && env_flag("B200_CG_FUSED_DOT_REMOTE", M > 6000000)) {
-        // by size: where the CG vectors live in L2 across the iteration (a few million rows per GPU) the separate
-        // dot pass costs less than the epilogues do -- 2 GPUs, 2.1 M rows each: 27-point 187.6 vs 200.3 us per
-        // iteration, symmetric 7-point 102.8 vs 110.4; at 16.8 M rows each: 1145.8 vs 1142.7 and 489.9 vs 469.3
+                 && env_flag("B200_CG_FUSED_DOT_REMOTE", true)) {
+        // 2 GPUs, us per iteration without / with (separate vector kernels): 2.1 M rows each, 27-point 172.7 / 172.8,
+        // symmetric 7-point 89.5 / 85.5; 16.8 M rows each: 1139.1 / 1127.3 and 475.9 / 446.2
         std::int32_t ok = 0;
         if (b200_csr_plan_rowlist_dot_ok(rem->op().plan(), &ok) == B200_OK && ok) {
           dot_local = loc;
@@ -273,11 +277,16 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     }
   }
   const bool have_dot = single != nullptr || sym_single != nullptr || dot_local != nullptr;
-  // vector half of the iteration in one cooperative launch: needs the peer mailboxes (or one rank); the
-  // NCCL fallback keeps the separate kernels.  Default: on when there is more than one rank (where the
-  // launch gaps between five small kernels cost more than they do at one rank); B200_CG_FUSED_VEC forces.
+  const bool wait_in_remote = env_flag("B200_CG_WAIT_IN_REMOTE", true);
+  // Vector half of the iteration: three kernels (dot [unless it rode in the SpMV], x/r update + r.r, p update) with
+  // the sums over the ranks in the tails of the first two (tail_ar), or ONE cooperative launch with grid-wide
+  // hand-overs (B200_CG_FUSED_VEC=1; needs the peer mailboxes or one rank).  Inside a captured graph the launch gaps
+  // the fused step was built to remove are gone, and its two in-kernel hand-overs (every CTA's ticket, the fold,
+  // the release) cost more than two kernel boundaries: 2 GPUs, 27-point, 2.1 M rows per GPU, 180.9 us per
+  // iteration fused against 173.5 with the three kernels; 16.8 M rows: 1142.9 against 1133.9.  Default: off.
+  const bool tail_ar = peer != nullptr && env_flag("B200_CG_TAIL_ALLREDUCE", true);
   const bool can_fuse = peer != nullptr || exec.comm_size() == 1;
-  const bool fused_vec = can_fuse && env_flag("B200_CG_FUSED_VEC", exec.comm_size() > 1);
+  const bool fused_vec = can_fuse && env_flag("B200_CG_FUSED_VEC", false);
   // CUDA graph of GRAPH_ITERS iterations: everything the iteration enqueues must be a kernel with
   // device-side state, i.e. the kernel-driven halo (or no halo) and no NCCL call
   const char* hm = col_l2g->halo_mode();
@@ -327,10 +336,18 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
                                             dot_local->values(), p, Ap, state + 1, stream),
                       "cg spmv+dot (local block)");
       mark(2);
-      col_l2g->update_finalise(p);
-      detail::check(b200_csr_spmv_rowlist_dot_f64(dot_remote->op().plan(), dot_local->op().plan(), dot_remote->rowptr(),
-                                                  dot_remote->colind(), dot_remote->values(), p, Ap, state + 1, stream),
+      // the remote product is also the halo's wait (ghost values straight from the staging slot) and carries the
+      // sum over the ranks in its tail
+      void* hw = wait_in_remote ? col_l2g->kernel_wait_desc() : nullptr;
+      if (hw == nullptr)
+        col_l2g->update_finalise(p);
+      detail::check(b200_csr_spmv_rowlist_dot_halo_f64(dot_remote->op().plan(), dot_local->op().plan(), dot_remote->rowptr(),
+                                                       dot_remote->colind(), dot_remote->values(), p, Ap, state + 1,
+                                                       (tail_ar && !fused_vec) ? peer : nullptr, hw, col_l2g->local_size(),
+                                                       stream),
                     "cg remote block + dot");
+      if (hw != nullptr)
+        col_l2g->finalised_by_kernel();
       mark(3);
     } else if (phases && A.remote_block() != nullptr) { // Matrix::mult, opened up to time its parts
       A.local_block()->mult(1, p, 0, Ap);
@@ -351,11 +368,18 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
                     "cg fused step");
       pushed_ahead = fused_push;
     } else {
-      if (!have_dot)
-        detail::check(b200_cg_dot_f64(M, p, Ap, state + 1, scratch, state + 4, stream), "cg dot");
-      allreduce(state + 1); // cg.cpp:65
-      detail::check(b200_cg_update_xr_f64(M, state, p, Ap, x_padded, r, stream), "cg update x,r");
-      allreduce(state + 2); // cg.cpp:75
+      // the sums over the ranks (cg.cpp:65,75) ride in the tail of the kernel that produces the value where the
+      // peer mailboxes exist (tail_ar); a launch of their own otherwise
+      if (!have_dot) {
+        detail::check(b200_cg_dot_peer_f64(M, p, Ap, state + 1, scratch, state + 4, tail_ar ? peer : nullptr, stream), "cg dot");
+        if (!tail_ar)
+          allreduce(state + 1);
+      } else if (!(dot_local && tail_ar)) { // (the two-block dot already summed over the ranks in its tail)
+        allreduce(state + 1);
+      }
+      detail::check(b200_cg_update_xr_peer_f64(M, state, p, Ap, x_padded, r, tail_ar ? peer : nullptr, stream), "cg update x,r");
+      if (!tail_ar)
+        allreduce(state + 2);
       detail::check(b200_cg_update_p_f64(M, state, r, p, hist, hist_len, stream), "cg update p");
     }
     mark(4);
@@ -397,7 +421,7 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
     iteration();
   bool graph_ready = false;
   if (!phases && use_graph && kmax > 1 && w.graph_mode != -2) {
-    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0) | (sym_single ? 4 : 0) | (fused_push ? 8 : 0) | (dot_local ? 16 : 0);
+    const int mode = (single ? 1 : 0) | (fused_vec ? 2 : 0) | (sym_single ? 4 : 0) | (fused_push ? 8 : 0) | (dot_local ? 16 : 0) | (tail_ar ? 32 : 0) | (wait_in_remote ? 64 : 0);
     graph_ready = w.graph != nullptr && w.graph_matrix == static_cast<const void*>(&A) && w.graph_mode == mode
                   && w.graph_epoch == detail::structure_epoch();
     if (!graph_ready) {
@@ -469,6 +493,18 @@ int cg(MPI_Comm comm, B200Executor& exec, const Matrix<double>& A, const double*
   detail::check(b200_stream_synchronize(stream), "cg sync");
   iterations = static_cast<int>(last.iter);
 
+  if (timeline) {
+    double tl[6];
+    int tl_rank = 0;
+    MPI_Comm_rank(comm, &tl_rank);
+    detail::check(b200_memcpy_d2h_async(tl, state + 10, sizeof(tl), stream), "timeline copy");
+    detail::check(b200_stream_synchronize(stream), "cg sync");
+    std::fprintf(stderr,
+                 "[cg timeline rank %d] last live fused step, CTA 0, us: dot pass %.1f | sum over ranks %.1f | x,r update "
+                 "%.1f | sum over ranks %.1f | p update %.1f | total %.1f\n",
+                 tl_rank, (tl[1] - tl[0]) * 1e-3, (tl[2] - tl[1]) * 1e-3, (tl[3] - tl[2]) * 1e-3,
+                 (tl[4] - tl[3]) * 1e-3, (tl[5] - tl[4]) * 1e-3, (tl[5] - tl[0]) * 1e-3);
+  }
   detail::check(b200_memcpy_d2d_async(x, x_padded, sizeof(double) * M, stream), "copy"); // cg.cpp:89
   if (residual_history) {
     residual_history->assign(iterations, 0.0);

@@ -42,17 +42,76 @@ static int vec_grid(int n)
   return std::max(1, std::min(want, cap));
 }
 
+// (PeerSlot / PeerDesc / peer_exchange_warp: common.cuh -- the SpMV epilogues exchange through them too)
 // Fold one dd value per thread over the whole grid into out[0] (deterministic, and in twice
 // the working precision: see common.cuh).  partials: 2 * plen doubles.
-__device__ __forceinline__ bool grid_sum(dd v, double* partials, int plen, unsigned int* counter, double* out)
+// The last CTA to arrive folds the per-CTA partials with all its warps: one warp alone (grid_dd_reduce, which the
+// SpMV epilogue keeps for its ~300 partials) walks the ~1200 of these grids in 37 dependent L2 round trips, a
+// tail of several microseconds on kernels that take ten.
+// peer != nullptr: the last CTA also exchanges the sum with the other ranks (peer_exchange_warp) and out[0] is the
+// sum over all of them -- the MPI_Allreduce of cg.cpp:65,75 in the tail of the kernel that produced the value,
+// instead of a launch of its own.
+__device__ __forceinline__ void grid_sum(dd v, double* partials, int plen, unsigned int* counter, double* out,
+                                         PeerDesc* peer = nullptr)
 {
-  __shared__ double s_warp[2 * (VEC_THREADS / 32)];
-  return grid_dd_reduce(v, threadIdx.x, VEC_THREADS, 1, s_warp, partials, plen, counter, out);
+  constexpr int NW = VEC_THREADS / 32;
+  __shared__ double s_warp[2 * NW];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  v = dd_warp_sum(v);
+  if (lane == 0) {
+    s_warp[2 * warp] = v.hi;
+    s_warp[2 * warp + 1] = v.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    if (lane == 0) {
+      partials[blockIdx.x] = t.hi;
+      partials[plen + blockIdx.x] = t.lo;
+      __threadfence();
+      s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+  }
+  __syncthreads();
+  if (!s_last)
+    return;
+  __threadfence();
+  dd s = {0.0, 0.0};
+  for (int i = tid; i < (int)gridDim.x; i += VEC_THREADS) {
+    dd w;
+    w.hi = __ldcg(partials + i);
+    w.lo = __ldcg(partials + plen + i);
+    s = dd_merge(s, w);
+  }
+  s = dd_warp_sum(s);
+  if (lane == 0) {
+    s_warp[2 * warp] = s.hi;
+    s_warp[2 * warp + 1] = s.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    double mine[B200_PEER_REDUCE_MAX_COUNT] = {__dadd_rn(t.hi, t.lo), 0.0, 0.0, 0.0};
+    double total[B200_PEER_REDUCE_MAX_COUNT] = {mine[0], 0.0, 0.0, 0.0};
+    if (peer != nullptr)
+      peer_exchange_warp(peer, lane, 1, mine, total);
+    if (lane == 0) {
+      out[0] = total[0];
+      *counter = 0u;
+    }
+  }
 }
 
 __global__ void __launch_bounds__(VEC_THREADS)
     dot_kernel(int n, const double* __restrict__ a, const double* __restrict__ b,
-               double* __restrict__ out, double* __restrict__ scratch, const double* done_flag)
+               double* __restrict__ out, double* __restrict__ scratch, const double* done_flag, PeerDesc* peer)
 {
   if (done_flag != nullptr && *done_flag != 0.0)
     return;
@@ -69,14 +128,14 @@ __global__ void __launch_bounds__(VEC_THREADS)
   }
   if ((n & 1) && tid == 0)
     dd_add_prod(acc, a[n - 1], b[n - 1]);
-  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out);
+  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out, peer);
 }
 
 // Unaligned fallback (pointer not 16-byte aligned): scalar loads.
 __global__ void __launch_bounds__(VEC_THREADS)
     dot_kernel_scalar(int n, const double* __restrict__ a, const double* __restrict__ b,
                       double* __restrict__ out, double* __restrict__ scratch,
-                      const double* done_flag)
+                      const double* done_flag, PeerDesc* peer)
 {
   if (done_flag != nullptr && *done_flag != 0.0)
     return;
@@ -84,7 +143,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const int stride = gridDim.x * blockDim.x;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     dd_add_prod(acc, __ldg(a + i), __ldg(b + i));
-  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out);
+  grid_sum(acc, scratch + 8, DOT_PARTIALS, reinterpret_cast<unsigned int*>(scratch), out, peer);
 }
 
 __global__ void init_state_kernel(double* st, const double* rr, double rtol, int kmax)
@@ -103,7 +162,7 @@ __global__ void init_state_kernel(double* st, const double* rr, double rtol, int
 
 __global__ void __launch_bounds__(VEC_THREADS)
     update_xr_kernel(int n, double* __restrict__ st, const double* __restrict__ p,
-                     const double* __restrict__ Ap, double* __restrict__ x, double* __restrict__ r)
+                     const double* __restrict__ Ap, double* __restrict__ x, double* __restrict__ r, PeerDesc* peer)
 {
   if (st[ST_DONE] != 0.0)
     return;
@@ -119,7 +178,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
     r[i] = ri;
     dd_add_prod(acc, ri, ri);                              // cg.cpp:73
   }
-  grid_sum(acc, st + ST_PARTIALS, DOT_PARTIALS, reinterpret_cast<unsigned int*>(st + ST_COUNTER), st + ST_RR);
+  grid_sum(acc, st + ST_PARTIALS, DOT_PARTIALS, reinterpret_cast<unsigned int*>(st + ST_COUNTER), st + ST_RR, peer);
 }
 
 __global__ void __launch_bounds__(VEC_THREADS)
@@ -158,71 +217,6 @@ __global__ void __launch_bounds__(VEC_THREADS)
   }
 }
 
-// ---------------------------------------------------------------------------
-// Scalar allreduce over peer memory (the MPI_Allreduce of cg.cpp:49,65,75 on device
-// scalars).  Every rank owns a mailbox in IPC-exported device memory: one slot per
-// (parity, source rank).  One warp per rank: lane q stores this rank's values and then
-// the sequence number (release, system scope) into rank q's mailbox over NVLink; lane q
-// then spins (acquire) on the slot rank q writes here.  The sum runs over the ranks in
-// rank order on every rank, so all ranks get the same bits.  Two parities: a rank can
-// only be one allreduce ahead of the slowest one (it needs that rank's current value
-// to finish), so the slot it overwrites has been consumed.
-// ---------------------------------------------------------------------------
-struct PeerSlot {
-  double v[B200_PEER_REDUCE_MAX_COUNT];
-  unsigned long long seq;
-  unsigned long long pad[3];
-};
-static_assert(sizeof(PeerSlot) == 64, "one slot per 64-byte line");
-
-struct PeerDesc {
-  int rank, world;
-  unsigned long long seq;
-  PeerSlot* box[B200_PEER_REDUCE_MAX_RANKS]; // box[q] = rank q's mailbox (box[rank]: mine, local)
-};
-
-// One full warp.  mine[k], k < count: this rank's values; returns the sums over the ranks (all lanes).
-__device__ __forceinline__ void peer_exchange_warp(PeerDesc* d, int lane, int count,
-                                                   const double (&mine)[B200_PEER_REDUCE_MAX_COUNT],
-                                                   double (&total)[B200_PEER_REDUCE_MAX_COUNT])
-{
-  const int rank = d->rank, world = d->world;
-  const unsigned long long seq = d->seq + 1;
-  const int par = (int)(seq & 1ull);
-  __syncwarp();
-  double got[B200_PEER_REDUCE_MAX_COUNT];
-#pragma unroll
-  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
-    got[k] = 0.0;
-  if (lane < world) {
-    PeerSlot* dst = d->box[lane] + par * world + rank;
-#pragma unroll
-    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
-      if (k < count)
-        asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&dst->v[k]), "d"(mine[k]) : "memory");
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->seq), "l"(seq) : "memory");
-    const PeerSlot* src = d->box[rank] + par * world + lane;
-    unsigned long long seen;
-    do {
-      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->seq) : "memory");
-    } while (seen != seq);
-#pragma unroll
-    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
-      if (k < count)
-        asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(got[k]) : "l"(&src->v[k]) : "memory");
-  }
-  __syncwarp();
-#pragma unroll
-  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
-    double t = 0.0;
-    for (int q = 0; q < world; ++q)
-      t = add_rn(t, __shfl_sync(0xffffffffu, got[k], q));
-    total[k] = t;
-  }
-  if (lane == 0)
-    d->seq = seq;
-}
-
 __global__ void __launch_bounds__(32) peer_allreduce_kernel(PeerDesc* d, double* val, int count)
 {
   const int lane = threadIdx.x;
@@ -253,6 +247,7 @@ __device__ __forceinline__ double fused_grid_allreduce(dd v, double* st, PeerDes
 {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int NW = VEC_THREADS / 32;
+  __shared__ bool s_last;
   double* partials = st + ST_PARTIALS;
   unsigned int* counter = reinterpret_cast<unsigned int*>(st + ST_COUNTER);
   unsigned int* gen = reinterpret_cast<unsigned int*>(st + ST_GEN);
@@ -267,25 +262,39 @@ __device__ __forceinline__ double fused_grid_allreduce(dd v, double* st, PeerDes
     t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
     t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
     t = dd_warp_sum(t);
-    unsigned int ticket = 0;
     if (lane == 0) {
       partials[blockIdx.x] = t.hi;
       partials[DOT_PARTIALS + blockIdx.x] = t.lo;
       __threadfence();
-      ticket = atomicAdd(counter, 1u);
+      s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
     }
-    ticket = __shfl_sync(0xffffffffu, ticket, 0);
-    if (ticket == gridDim.x - 1) { // the last CTA: fold, exchange, publish
-      __threadfence();
-      dd s = {0.0, 0.0};
-      for (int i = lane; i < (int)gridDim.x; i += 32) {
-        dd w;
-        w.hi = __ldcg(partials + i);
-        w.lo = __ldcg(partials + DOT_PARTIALS + i);
-        s = dd_merge(s, w);
-      }
-      s = dd_warp_sum(s);
-      double mine[B200_PEER_REDUCE_MAX_COUNT] = {__dadd_rn(s.hi, s.lo), 0.0, 0.0, 0.0};
+  }
+  __syncthreads();
+  if (s_last) {
+    // The last CTA to arrive folds the partials with ALL its warps (one warp alone walked ~1200 partials in 37
+    // dependent L2 round trips: 8-9 us of the hand-over, twice per iteration), exchanges the sum with the other
+    // ranks, stores the global value and releases the generation.
+    __threadfence();
+    dd s = {0.0, 0.0};
+    for (int i = tid; i < (int)gridDim.x; i += VEC_THREADS) {
+      dd w;
+      w.hi = __ldcg(partials + i);
+      w.lo = __ldcg(partials + DOT_PARTIALS + i);
+      s = dd_merge(s, w);
+    }
+    s = dd_warp_sum(s);
+    __syncthreads(); // s_warp: everybody has read its warp's slot above
+    if (lane == 0) {
+      s_warp[2 * warp] = s.hi;
+      s_warp[2 * warp + 1] = s.lo;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      dd t;
+      t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+      t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
+      t = dd_warp_sum(t);
+      double mine[B200_PEER_REDUCE_MAX_COUNT] = {__dadd_rn(t.hi, t.lo), 0.0, 0.0, 0.0};
       double total[B200_PEER_REDUCE_MAX_COUNT] = {mine[0], 0.0, 0.0, 0.0};
       if (peer != nullptr)
         peer_exchange_warp(peer, lane, 1, mine, total);
@@ -296,13 +305,16 @@ __device__ __forceinline__ double fused_grid_allreduce(dd v, double* st, PeerDes
         asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(gen), "r"(gen_target) : "memory");
       }
     }
-    if (lane == 0) {
-      unsigned int seen;
-      do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(gen) : "memory");
-      } while ((int)(seen - gen_target) < 0);
-      *s_bcast = __ldcg(st + ST_PARTIALS + 2 * DOT_PARTIALS);
+  }
+  if (tid == 0) {
+    unsigned int seen;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(gen) : "memory");
+      if ((int)(seen - gen_target) >= 0)
+        break;
+      __nanosleep(64); // ~1200 CTAs poll one word: leave the L2 slice some room for the last CTA's fold
     }
+    *s_bcast = __ldcg(st + ST_PARTIALS + 2 * DOT_PARTIALS);
   }
   __syncthreads();
   const double out = *s_bcast;
@@ -362,6 +374,16 @@ __global__ void __launch_bounds__(VEC_THREADS)
   const double rnorm_old = st[ST_RNORM_OLD], rnorm0 = st[ST_RNORM0], rtol = st[ST_RTOL];
   const int stride = gridDim.x * blockDim.x;
   const int tid0 = blockIdx.x * blockDim.x + threadIdx.x;
+  // B200_CG_TIMELINE (host/cg.cpp sets st[9]): CTA 0 leaves %globaltimer stamps of its phases in st[10..15]
+  const bool timeline = st[9] != 0.0;
+  auto stamp = [&](int k) {
+    if (timeline && tid0 == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      st[10 + k] = (double)t;
+    }
+  };
+  stamp(0);
 
   // 16-byte accesses when the vectors allow it (they come from cudaMalloc: always, unless a caller offsets them)
   const bool vec2 = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(Ap) | reinterpret_cast<uintptr_t>(x)
@@ -382,6 +404,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
     }
     for (int i = 2 * n2 + tid0; i < n; i += stride)
       dd_add_prod(acc, p[i], Ap[i]);
+    stamp(1);
     pAp = fused_grid_allreduce(acc, st, peer, gen0 + 1, s_warp, &s_bcast);
   } else if (peer != nullptr) { // the SpMV epilogue left this rank's p.Ap in st[ST_PAP]
     dd acc = {0.0, 0.0};
@@ -391,6 +414,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
   } else {
     pAp = st[ST_PAP];
   }
+  stamp(2);
   const double alpha = (rnorm_old * rnorm_old) / pAp; // cg.cpp:66
   const double nalpha = -alpha;
   dd acc = {0.0, 0.0};
@@ -413,7 +437,9 @@ __global__ void __launch_bounds__(VEC_THREADS)
     r[i] = ri;
     dd_add_prod(acc, ri, ri);
   }
+  stamp(3);
   const double rr = fused_grid_allreduce(acc, st, peer, gen0 + 2, s_warp, &s_bcast);
+  stamp(4);
   const double rnorm_new = sqrt(rr);                                      // cg.cpp:76
   const double beta = (rnorm_new * rnorm_new) / (rnorm_old * rnorm_old);  // cg.cpp:77
   const bool converged = (rnorm_new / rnorm0) < rtol;                     // cg.cpp:80
@@ -428,6 +454,7 @@ __global__ void __launch_bounds__(VEC_THREADS)
     for (int i = 2 * n2 + tid0; i < n; i += stride)
       p[i] = __dadd_rn(__dmul_rn(beta, p[i]), r[i]);
   }
+  stamp(5);
   if (tid0 == 0) { // nobody reads these again in this launch (everybody took its copies above)
     const int iter = (int)st[ST_ITER] + 1;
     st[ST_ITER] = (double)iter;
@@ -467,18 +494,23 @@ extern "C" {
 int b200_cg_dot_f64(int32_t n, const double* d_a, const double* d_b, double* d_out,
                     double* d_scratch, const double* d_done_flag, void* stream)
 {
+  return b200_cg_dot_peer_f64(n, d_a, d_b, d_out, d_scratch, d_done_flag, nullptr, stream);
+}
+
+int b200_cg_dot_peer_f64(int32_t n, const double* d_a, const double* d_b, double* d_out, double* d_scratch,
+                         const double* d_done_flag, void* peer_ctx, void* stream)
+{
   B200_REQUIRE(n >= 0 && d_out && d_scratch, "bad argument");
   B200_REQUIRE(n == 0 || (d_a && d_b), "NULL vector");
   if (int rc = need_gpu())
     return rc;
+  PeerDesc* peer = static_cast<PeerDesc*>(peer_ctx);
   const int grid = std::min(vec_grid(n), B200_DOT_SCRATCH_DOUBLES - 8);
   const bool al = ((reinterpret_cast<uintptr_t>(d_a) | reinterpret_cast<uintptr_t>(d_b)) & 15) == 0;
   if (al)
-    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch,
-                                                            d_done_flag);
+    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch, d_done_flag, peer);
   else
-    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch,
-                                                                   d_done_flag);
+    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, d_scratch, d_done_flag, peer);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -496,12 +528,18 @@ int b200_cg_init_state(double* d_state, const double* d_rr, double rtol, int32_t
 int b200_cg_update_xr_f64(int32_t n, double* d_state, const double* d_p, const double* d_Ap,
                           double* d_x, double* d_r, void* stream)
 {
+  return b200_cg_update_xr_peer_f64(n, d_state, d_p, d_Ap, d_x, d_r, nullptr, stream);
+}
+
+int b200_cg_update_xr_peer_f64(int32_t n, double* d_state, const double* d_p, const double* d_Ap, double* d_x,
+                               double* d_r, void* peer_ctx, void* stream)
+{
   B200_REQUIRE(n >= 0 && d_state, "bad argument");
   B200_REQUIRE(n == 0 || (d_p && d_Ap && d_x && d_r), "NULL vector");
   if (int rc = need_gpu())
     return rc;
-  update_xr_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_p, d_Ap, d_x,
-                                                                       d_r);
+  update_xr_kernel<<<vec_grid(n), VEC_THREADS, 0, as_stream(stream)>>>(n, d_state, d_p, d_Ap, d_x, d_r,
+                                                                       static_cast<PeerDesc*>(peer_ctx));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -679,9 +717,9 @@ extern "C" int b200_cg_dot_static_f64(int32_t n, const double* d_a, const double
   const int grid = std::min(vec_grid(n), B200_DOT_SCRATCH_DOUBLES - 8);
   const bool al = ((reinterpret_cast<uintptr_t>(d_a) | reinterpret_cast<uintptr_t>(d_b)) & 15) == 0;
   if (al)
-    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr);
+    dot_kernel<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr, nullptr);
   else
-    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr);
+    dot_kernel_scalar<<<grid, VEC_THREADS, 0, as_stream(stream)>>>(n, d_a, d_b, d_out, scratch, nullptr, nullptr);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -323,4 +323,70 @@ struct HaloDesc {
   char* my_slot[2];
 };
 
+// ---------------------------------------------------------------------------
+// Scalar allreduce over peer memory (the MPI_Allreduce of cg.cpp:49,65,75 on device
+// scalars).  Every rank owns a mailbox in IPC-exported device memory: one slot per
+// (parity, source rank).  One warp per rank: lane q stores this rank's values and then
+// the sequence number (release, system scope) into rank q's mailbox over NVLink; lane q
+// then spins (acquire) on the slot rank q writes here.  The sum runs over the ranks in
+// rank order on every rank, so all ranks get the same bits.  Two parities: a rank can
+// only be one allreduce ahead of the slowest one (it needs that rank's current value
+// to finish), so the slot it overwrites has been consumed.
+// ---------------------------------------------------------------------------
+struct PeerSlot {
+  double v[B200_PEER_REDUCE_MAX_COUNT];
+  unsigned long long seq;
+  unsigned long long pad[3];
+};
+static_assert(sizeof(PeerSlot) == 64, "one slot per 64-byte line");
+
+struct PeerDesc {
+  int rank, world;
+  unsigned long long seq;
+  PeerSlot* box[B200_PEER_REDUCE_MAX_RANKS]; // box[q] = rank q's mailbox (box[rank]: mine, local)
+};
+
+// One full warp.  mine[k], k < count: this rank's values; returns the sums over the ranks (all lanes).
+__device__ __forceinline__ void peer_exchange_warp(PeerDesc* d, int lane, int count,
+                                                   const double (&mine)[B200_PEER_REDUCE_MAX_COUNT],
+                                                   double (&total)[B200_PEER_REDUCE_MAX_COUNT])
+{
+  const int rank = d->rank, world = d->world;
+  const unsigned long long seq = d->seq + 1;
+  const int par = (int)(seq & 1ull);
+  __syncwarp();
+  double got[B200_PEER_REDUCE_MAX_COUNT];
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+    got[k] = 0.0;
+  if (lane < world) {
+    PeerSlot* dst = d->box[lane] + par * world + rank;
+#pragma unroll
+    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+      if (k < count)
+        asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(&dst->v[k]), "d"(mine[k]) : "memory");
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->seq), "l"(seq) : "memory");
+    const PeerSlot* src = d->box[rank] + par * world + lane;
+    unsigned long long seen;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->seq) : "memory");
+    } while (seen != seq);
+#pragma unroll
+    for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k)
+      if (k < count)
+        asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(got[k]) : "l"(&src->v[k]) : "memory");
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < B200_PEER_REDUCE_MAX_COUNT; ++k) {
+    double t = 0.0;
+    for (int q = 0; q < world; ++q)
+      t = add_rn(t, __shfl_sync(0xffffffffu, got[k], q));
+    total[k] = t;
+  }
+  if (lane == 0)
+    d->seq = seq;
+}
+
+
 } // namespace b200

@@ -9,6 +9,7 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200
@@ -159,7 +160,13 @@ static int run_halo_push(void* desc, int32_t n, const int32_t* d_idx, const T* d
     return B200_ECUDA;
   }
   const int threads = 256;
-  const int blocks = std::max(1, std::min((n + threads - 1) / threads, num_sms() * 4));
+  static const int cap = [] {
+    const char* e = std::getenv("B200_HALO_PUSH_CTAS");
+    return (e && *e) ? std::atoi(e) : 0;
+  }();
+  // four elements per thread: every CTA ends with a system-scope fence and a ticket, and 512 of them for a
+  // 131072-entry halo cost more than they moved (2 GPUs, CG iteration 175.0 us with 512 CTAs, 171.7 with 128)
+  const int blocks = std::max(1, std::min((n + 4 * threads - 1) / (4 * threads), cap > 0 ? cap : num_sms() * 4));
   halo_push_kernel<T><<<blocks, threads, 0, as_stream(stream)>>>(static_cast<HaloDesc*>(desc), n, d_idx, d_x);
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -1325,23 +1325,45 @@ __global__ void spmv_rowlist_mixed_kernel(int n, const int32_t* __restrict__ row
 //         error-free products summed in twice the working precision the total is sum_r x_r * y_final[r] to
 //         ~1e-32 -- the same double a single dot product over the final y rounds to;
 //   c_r = x_r * (row sum)                   symmetric local block (its epilogue holds x'A_local x already).
+// halo != nullptr: the kernel is also the WAIT half of the kernel-driven halo exchange (halo.cu): every CTA polls
+//   this rank's flag words until each neighbour has published the epoch, and the ghost entries of x (columns >=
+//   ghost_base) are read straight from the staging slot the neighbours wrote -- no unpack launch, no ghost-tail
+//   round trip (the tail of x is left as it was).
+// peer != nullptr: the last CTA also exchanges the total with the other ranks (the MPI_Allreduce of cg.cpp:65).
 template <bool SYMLOCAL>
 __global__ void __launch_bounds__(128)
     spmv_rowlist_dot_kernel(int n, const int32_t* __restrict__ rowlist, const int32_t* __restrict__ rowptr,
                             const int32_t* __restrict__ colind, const double* __restrict__ val,
                             const double* __restrict__ x, double* __restrict__ y, const double* __restrict__ base,
                             int base_plen, int nbase, double* __restrict__ part, int plen, unsigned int* counter,
-                            double* __restrict__ dot_out)
+                            double* __restrict__ dot_out, PeerDesc* peer, const HaloDesc* halo, int ghost_base)
 {
-  __shared__ double s_warp[2 * 4];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NT = 128, NW = NT / 32;
+  __shared__ double s_warp[2 * NW];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double* xg = x; // xg[c] = x[c] for ghost columns
+  if (halo != nullptr) {
+    const unsigned int epoch = halo->epoch; // the push of this exchange precedes us on the stream
+    if (tid < halo->nnbr) {
+      unsigned int seen;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(halo->my_flag[tid]) : "memory");
+      } while ((int)(seen - epoch) < 0);
+    }
+    __syncthreads();
+    xg = reinterpret_cast<const double*>(halo->my_slot[epoch & 1u]) - ghost_base;
+  }
   dd dot = {0.0, 0.0};
-  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+  for (int k = blockIdx.x * NT + tid; k < n; k += gridDim.x * NT) {
     const int r = __ldg(rowlist + k);
     const int rs = __ldg(rowptr + r), re = __ldg(rowptr + r + 1);
     double sum = 0;
-    for (int j = rs; j < re; ++j)
-      sum = add_rn(sum, mul_rn(__ldg(val + j), __ldg(x + __ldg(colind + j))));
+    for (int j = rs; j < re; ++j) {
+      const int c = __ldg(colind + j);
+      const double xv = c >= ghost_base ? __ldcg(xg + c) : __ldg(x + c);
+      sum = add_rn(sum, mul_rn(__ldg(val + j), xv));
+    }
     const double yo = y[r];
     const double yn = add_rn(sum, yo);
     y[r] = yn;
@@ -1361,37 +1383,52 @@ __global__ void __launch_bounds__(128)
   __syncthreads();
   if (warp == 0) {
     dd t;
-    t.hi = lane < 4 ? s_warp[2 * lane] : 0.0;
-    t.lo = lane < 4 ? s_warp[2 * lane + 1] : 0.0;
+    t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
     t = dd_warp_sum(t);
-    unsigned int ticket = 0;
     if (lane == 0) {
       part[blockIdx.x] = t.hi;
       part[plen + blockIdx.x] = t.lo;
       __threadfence();
-      ticket = atomicAdd(counter, 1u);
+      s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
     }
-    ticket = __shfl_sync(0xffffffffu, ticket, 0);
-    if (ticket == gridDim.x - 1) {
-      __threadfence();
-      dd s = {0.0, 0.0};
-      for (int i = lane; i < nbase; i += 32) {
-        dd w;
-        w.hi = __ldcg(base + i);
-        w.lo = __ldcg(base + base_plen + i);
-        s = dd_merge(s, w);
-      }
-      for (int i = lane; i < (int)gridDim.x; i += 32) {
-        dd w;
-        w.hi = __ldcg(part + i);
-        w.lo = __ldcg(part + plen + i);
-        s = dd_merge(s, w);
-      }
-      s = dd_warp_sum(s);
-      if (lane == 0) {
-        dot_out[0] = __dadd_rn(s.hi, s.lo);
-        *counter = 0u;
-      }
+  }
+  __syncthreads();
+  if (!s_last)
+    return;
+  // the last CTA folds the local block's partials and this grid's with all its warps
+  __threadfence();
+  dd s = {0.0, 0.0};
+  for (int i = tid; i < nbase; i += NT) {
+    dd w;
+    w.hi = __ldcg(base + i);
+    w.lo = __ldcg(base + base_plen + i);
+    s = dd_merge(s, w);
+  }
+  for (int i = tid; i < (int)gridDim.x; i += NT) {
+    dd w;
+    w.hi = __ldcg(part + i);
+    w.lo = __ldcg(part + plen + i);
+    s = dd_merge(s, w);
+  }
+  s = dd_warp_sum(s);
+  if (lane == 0) {
+    s_warp[2 * warp] = s.hi;
+    s_warp[2 * warp + 1] = s.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    dd t;
+    t.hi = lane < NW ? s_warp[2 * lane] : 0.0;
+    t.lo = lane < NW ? s_warp[2 * lane + 1] : 0.0;
+    t = dd_warp_sum(t);
+    double mine[B200_PEER_REDUCE_MAX_COUNT] = {__dadd_rn(t.hi, t.lo), 0.0, 0.0, 0.0};
+    double total[B200_PEER_REDUCE_MAX_COUNT] = {mine[0], 0.0, 0.0, 0.0};
+    if (peer != nullptr)
+      peer_exchange_warp(peer, lane, 1, mine, total);
+    if (lane == 0) {
+      dot_out[0] = total[0];
+      *counter = 0u;
     }
   }
 }
@@ -2178,6 +2215,14 @@ int b200_csr_plan_rowlist_dot_ok(void* plan, int32_t* ok)
 int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr, const int32_t* d_colind,
                                   const double* d_val, const double* d_x, double* d_y, double* d_dot, void* stream)
 {
+  return b200_csr_spmv_rowlist_dot_halo_f64(remote_plan, local_plan, d_rowptr, d_colind, d_val, d_x, d_y, d_dot, nullptr,
+                                            nullptr, 0, stream);
+}
+
+int b200_csr_spmv_rowlist_dot_halo_f64(void* remote_plan, void* local_plan, const int32_t* d_rowptr,
+                                       const int32_t* d_colind, const double* d_val, const double* d_x, double* d_y,
+                                       double* d_dot, void* peer_ctx, void* halo_desc, int32_t ghost_base, void* stream)
+{
   B200_REQUIRE(remote_plan && local_plan && d_dot, "NULL argument");
   const Plan& p = *static_cast<const Plan*>(remote_plan);
   const Plan& l = *static_cast<const Plan*>(local_plan);
@@ -2185,6 +2230,7 @@ int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int
                "rowlist dot: the block needs a row list of short rows (b200_csr_plan_rowlist_dot_ok)");
   B200_REQUIRE(d_rowptr && d_colind && d_val && d_x && d_y, "NULL array");
   B200_REQUIRE(l.num_tiles > 0 && l.variant == 0 && l.d_partials != nullptr, "rowlist dot: the local plan ran no dot epilogue");
+  B200_REQUIRE(halo_desc == nullptr || ghost_base >= 0, "rowlist dot: bad ghost base");
   if (num_sms() <= 0) {
     set_error("no CUDA device available: this build has no CPU path");
     return B200_ECUDA;
@@ -2194,13 +2240,18 @@ int b200_csr_spmv_rowlist_dot_f64(void* remote_plan, void* local_plan, const int
   B200_REQUIRE(nbase <= l.partials_len, "partials too small");
   const int n = p.n_rowlist;
   const int grid = std::max(1, std::min((n + 127) / 128, p.partials_len));
+  const int gb = halo_desc ? ghost_base : 0x7fffffff; // no halo: every column reads x
   cudaStream_t st = as_stream(stream);
+  PeerDesc* peer = static_cast<PeerDesc*>(peer_ctx);
+  const HaloDesc* halo = static_cast<const HaloDesc*>(halo_desc);
   if (l.symmetric)
     spmv_rowlist_dot_kernel<true><<<grid, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x, d_y, l.d_partials,
-                                                        l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot);
+                                                        l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot,
+                                                        peer, halo, gb);
   else
     spmv_rowlist_dot_kernel<false><<<grid, 128, 0, st>>>(n, p.d_rowlist, d_rowptr, d_colind, d_val, d_x, d_y, l.d_partials,
-                                                         l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot);
+                                                         l.partials_len, nbase, p.d_partials, p.partials_len, p.d_counter, d_dot,
+                                                         peer, halo, gb);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
