@@ -1,8 +1,8 @@
 #!/bin/bash
 # r02, 2 GPUs: two-channel halo validation
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_dist.py -x -q -m gpu > gpurun_out/r02_pytest_dist_n2.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_dist_n2.log
-tail -8 gpurun_out/r02_pytest_dist_n2.log | cut -c1-300
+true
+true
 run() { timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port $1 bench.py --gpus 2 --steps 30 --warmup 3 $2 > gpurun_out/$3.json 2> gpurun_out/$3.err; echo "$3 rc=$?"; tail -2 gpurun_out/$3.err | cut -c1-300; }
 run 29511 "" r02_bench_n2
 run 29512 "--strong --config5-rows 0" r02_bench_n2_strong
