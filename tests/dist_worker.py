@@ -168,6 +168,25 @@ def main():
                         # shim's MPI_Allreduce there): the GPU follows the reference's trajectory exactly at any rank count
                         check(it == ref["cg_it"] and np.array_equal(xs.cpu().numpy(), xr),
                               tag + f": cg not bit-identical to the reference (its {it} vs {ref['cg_it']}, err {err})")
+                    if kind in ("lap27", "lap7") and cm == api.P2P_NONBLOCKING:
+                        # every switch of host/cg.cpp away from its default: same trajectory
+                        for envs in ({"B200_CG_FUSED_VEC": "1"}, {"B200_CG_FUSED_VEC": "1", "B200_CG_FUSED_PUSH": "1"},
+                                     {"B200_CG_FUSED_VEC": "1", "B200_CG_FUSED_DOT_REMOTE": "0"},
+                                     {"B200_CG_TAIL_ALLREDUCE": "0"}, {"B200_CG_FUSED_DOT_REMOTE": "0"},
+                                     {"B200_CG_WAIT_IN_REMOTE": "0"}, {"B200_CG_GRAPH": "0"},
+                                     {"B200_CG_FUSED_DOT": "1"}, {"B200_CG_FUSED_DOT": "0"}):
+                            os.environ.update(envs)
+                            try:
+                                xs2 = torch.zeros_like(b)
+                                it2, _ = api.cg(ex, A, b, xs2, want_cg[0], want_cg[1], history=True)
+                            finally:
+                                for k in envs:
+                                    os.environ.pop(k, None)
+                            if sym:
+                                e2 = np.linalg.norm(xs2.cpu().numpy() - xr) / max(np.linalg.norm(xr), 1e-300)
+                                check(abs(it2 - it) <= 1 and e2 < 1e-7, tag + f" {envs}: cg its {it2} vs {it}, err {e2}")
+                            else:
+                                check(it2 == it and torch.equal(xs2, xs), tag + f" {envs}: cg differs from the default path")
             A.close()
 
     # device-side builder (demos/CreateLaplace3D.h) against create_matrix on host-generated rows
