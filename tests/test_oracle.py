@@ -343,3 +343,33 @@ def test_bench_cpu_legs_run():
     assert mp["ms_per_step"] > 0 and mp["ranks"] >= 1
     om = CL.omp_spmv(7, True, nz=4, budget_s=0.2)
     assert om["kind"] == "reference" and om["rows"] == 256 * 256 * 4
+
+
+def test_quadratic_form_identity_behind_the_symmetric_dot_epilogue():
+    """b200_csr_symv_dot_f64 (kernels/spmv_csr.cu: dot_row) never sees a finished y row, so it sums
+    x_r (2 s_r - d_r x_r) with s_r = d_r x_r + sum_{c<r} a_rc x_c, the row sum of the lower + diagonal storage
+    (csr_kernels.cpp:28-38 forms the same s_r before it scatters).  Checked here on the oracle's own symmetric
+    kernel: the identity equals x . symv(x) to rounding, on a stencil and on irregular rows."""
+    import math
+    from spmv_b200 import synth
+    from tests.fixtures import split_symmetric
+    rng = np.random.default_rng(31)
+    cases_ = []
+    rp, col, val = synth.laplace3d_rows(9, 8, 7, 0, 7, 7)
+    cases_.append(split_symmetric(rp, col, val))
+    n = 3000
+    rp0, col0, val0 = synth.powerlaw_rows(n, 0, n, band=256)
+    S = sp.csr_matrix((val0, col0, rp0), shape=(n, n))
+    S = (S + S.T).tocsr()
+    S.sort_indices()
+    cases_.append(split_symmetric(S.indptr, S.indices, S.data))
+    for srp, sci, sv, d in cases_:
+        m = len(d)
+        x = rng.standard_normal(m)
+        y = K.symv(srp, sci, sv, d, x)                                  # the reference's symmetric product
+        low = sp.csr_matrix((sv, sci, srp), shape=(m, m)) @ x            # sum_{c<r} a_rc x_c
+        s_r = d * x + low
+        ident = math.fsum((x * (2.0 * s_r - d * x)).tolist())
+        direct = math.fsum((x * y).tolist())
+        scale = float(np.abs(x) @ (np.abs(sp.csr_matrix((np.abs(sv), sci, srp), shape=(m, m))) @ np.abs(x))) * 2 + float(np.abs(d) @ (x * x))
+        assert abs(ident - direct) <= 1e-13 * scale
