@@ -786,7 +786,7 @@ def measure_cusparse_powerlaw(api, dev, rows=3_000_000, steps=20):
 def measure_cublas_blas1(dev, m, iters=20):
     """The vector half of one iteration of the reference's CUDA CG (cuda/cg.cuda.cu:88-150): cublasDdot x2,
     cublasDaxpy x3, cublasDscal x1 with device pointer mode, on vectors of m doubles.  Library code, context
-    only: what this repo's three (or one fused) vector kernels replace."""
+    only: what this repo's three vector kernels replace."""
     try:
         import ctypes as C
         import glob
