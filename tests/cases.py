@@ -71,3 +71,41 @@ PLAN_KEYS = ("ranges", "ghosts", "neighbours", "send_count", "recv_count", "send
 
 def same_plan(a, b):
     return all(np.array_equal(a[k], b[k]) for k in PLAN_KEYS)
+
+
+def random_uneven_inputs(seed, size=None):
+    """Seeded random sparsity on an UNEVEN row partition: per-rank create_matrix inputs (the keys of
+    local_inputs) for `size` ranks (2 - 6, drawn from the seed when None).  One rank owns a single row; with
+    seed % 3 == 0 the last rank ghosts nothing.  Rows are sorted and de-duplicated, values standard normal."""
+    from spmv_b200 import synth
+    rng = np.random.default_rng(1000 + seed)
+    drawn = int(rng.integers(2, 7))
+    size = drawn if size is None else size
+    sizes = rng.integers(1, 300, size=size)
+    sizes[rng.integers(0, size)] = 1
+    ranges = np.concatenate([[0], np.cumsum(sizes)])
+    n = int(ranges[-1])
+    inps = []
+    for r in range(size):
+        r0, r1 = int(ranges[r]), int(ranges[r + 1])
+        m = r1 - r0
+        if seed % 3 == 0 and r == size - 1:
+            lens = rng.integers(1, 4, size=m)
+            gcol = np.concatenate([rng.integers(r0, r1, size=k) for k in lens])
+        else:
+            lens = rng.integers(0, 9, size=m)
+            tot = int(lens.sum())
+            near = rng.integers(max(0, r0 - 40), min(n, r1 + 40), size=tot)
+            far = rng.integers(0, n, size=tot)
+            gcol = np.where(rng.random(tot) < 0.8, near, far)
+        rows_of = np.repeat(np.arange(m), lens)
+        order = np.lexsort((gcol, rows_of))
+        rows_of, gcol = rows_of[order], gcol[order]
+        keep = np.ones(len(gcol), bool)
+        keep[1:] = (rows_of[1:] != rows_of[:-1]) | (gcol[1:] != gcol[:-1])
+        rows_of, gcol = rows_of[keep], gcol[keep]
+        rowptr = np.concatenate([[0], np.cumsum(np.bincount(rows_of, minlength=m))]).astype(np.int32)
+        lcol, ghosts = synth.localize_columns(gcol.astype(np.int64), r0, r1)
+        inps.append({"rowptr": rowptr, "colind": lcol, "values": rng.standard_normal(len(lcol)), "nrows_local": m,
+                     "ncols_local": m, "col_ghosts": ghosts, "r0": r0, "r1": r1})
+    return inps

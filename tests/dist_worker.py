@@ -189,6 +189,34 @@ def main():
                                 check(it2 == it and torch.equal(xs2, xs), tag + f" {envs}: cg differs from the default path")
             A.close()
 
+    # uneven partitions, a one-row rank, a rank that ghosts nothing (host logic only: plan + block split of the
+    # product's create_matrix against the message-free restatement and the reference's own code)
+    if mode == "cpu":
+        from oracle import plan as OP
+        for seed in range(4):
+            inps = cases.random_uneven_inputs(seed, size)
+            want = OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps])[rank]
+            ref_blocks = {}
+            if have_ref:
+                def body(q, inps=inps, ref_blocks=ref_blocks):
+                    i = inps[q]
+                    B = R.RefMatrix.create_matrix(i["rowptr"], i["colind"], i["values"], i["nrows_local"], i["ncols_local"],
+                                                  [], i["col_ghosts"], False, api.P2P_NONBLOCKING)
+                    ref_blocks[q] = (B.plan(0), B.block(0), B.block(1))
+                    B.close()
+                R.run_ranks(size, body)
+            inp = inps[rank]
+            for cm in (api.COLLECTIVE_BLOCKING, api.P2P_NONBLOCKING):
+                tag = f"random uneven seed={seed} size={size} cm={cm}"
+                A = api.Matrix.create_matrix(ex, inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                             inp["ncols_local"], [], inp["col_ghosts"], False, cm)
+                check(cases.same_plan(A.col_map().plan(), want), tag + ": plan differs from the restatement")
+                if have_ref and cm == api.P2P_NONBLOCKING:
+                    check(cases.same_plan(A.col_map().plan(), ref_blocks[rank][0]), tag + ": plan differs from the reference")
+                    check(cases.same_block(A.local_block(), ref_blocks[rank][1]), tag + ": local block differs")
+                    check(cases.same_block(A.remote_block(), ref_blocks[rank][2]), tag + ": remote block differs")
+                A.close()
+
     # device-side builder (demos/CreateLaplace3D.h) against create_matrix on host-generated rows
     if mode == "gpu":
         nx, ny, nz = 6, 5, 8 * size if size not in (1, 2, 4, 8) else 8

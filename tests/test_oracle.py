@@ -287,6 +287,49 @@ def test_plan_message_free_restatement_equals_reference(kind, n, size):
 
 
 @needs_ref
+@pytest.mark.parametrize("seed", range(6))
+def test_plan_and_halo_on_random_uneven_partitions(seed):
+    """Seeded random sparsity on UNEVEN row partitions (ranks of 1 row next to ranks of hundreds, ranks that ghost
+    nothing, ranks nobody ghosts, 2 - 6 ranks): the reference's L2GMap.cpp under thread-ranks against the
+    message-free restatement -- plan artefacts, update and reverse_update, bit for bit."""
+    from oracle import plan as OP
+    from oracle import ref_api as R
+    from spmv_b200 import synth
+    from tests import cases
+    if not R.available():
+        pytest.skip("oracle/_ref/libspmv_ref.so not built")
+    inps = cases.random_uneven_inputs(seed)
+    size = len(inps)
+    rng = np.random.default_rng(seed)
+    plans = OP.plans([i["ncols_local"] for i in inps], [i["col_ghosts"] for i in inps])
+    vec0 = [rng.standard_normal(p["local_size"] + p["num_ghosts"]) for p in plans]
+    got, fwd, rev = {}, {}, {}
+
+    def body(rank):
+        inp = inps[rank]
+        A = R.RefMatrix.create_matrix(inp["rowptr"], inp["colind"], inp["values"], inp["nrows_local"],
+                                      inp["ncols_local"], [], inp["col_ghosts"], False, 2)
+        got[rank] = A.plan(0)
+        x = vec0[rank].copy()
+        A.update(x)
+        fwd[rank] = x
+        z = vec0[rank].copy()
+        A.reverse_update(z)
+        rev[rank] = z
+        A.close()
+
+    R.run_ranks(size, body)
+    want_f = [v.copy() for v in vec0]
+    OP.update(plans, want_f)
+    want_r = [v.copy() for v in vec0]
+    OP.reverse_update(plans, want_r)
+    for r in range(size):
+        assert cases.same_plan(plans[r], got[r]), (seed, r)
+        assert np.array_equal(fwd[r], want_f[r]), (seed, r)
+        assert np.array_equal(rev[r], want_r[r]), (seed, r)
+
+
+@needs_ref
 @pytest.mark.parametrize("kind,n", [("fixture", None), ("lap7", (4, 3, 6)), ("powerlaw", 4000)])
 @pytest.mark.parametrize("size", [1, 2, 3])
 def test_halo_data_movement_restated_equals_reference(kind, n, size):
