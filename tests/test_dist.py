@@ -33,7 +33,7 @@ def _launch(mode, nproc, timeout=900):
     assert res.returncode == 0 and "DIST_OK" in res.stdout, res.stdout[-4000:]
 
 
-@pytest.mark.parametrize("nproc", [2, 3])
+@pytest.mark.parametrize("nproc", [2, 3, 5])
 def test_host_logic_gloo(nproc):
     _launch("cpu", nproc)
 
